@@ -1,0 +1,142 @@
+"""The CPU oracle (oracle/poisson_oracle.c) against the committed golden fixtures that were
+generated from the reference itself, and -- when oracle/_ref is present -- against the
+reference's own compiled code, live. Operators: bit-exact. Whole solves: iteration counts
+exact; norms within 1e-10 relative (north_star's fp64 tolerance)."""
+import numpy as np
+import pytest
+
+from oracle_lib import seeded_field
+
+RTOL = 1e-10  # north_star: "solution and residual norms within 1e-10 relative in fp64"
+
+
+def rel(a, b):
+    return abs(a - b) / max(abs(b), 1e-300)
+
+
+def test_process_grid_and_decomposition(oracle, golden):
+    for p, want in golden["process_grid"].items():
+        assert list(oracle.process_grid(int(p))) == want
+    for key, blocks in golden["decompose"].items():
+        mn, p = key.split("@")
+        m, n = map(int, mn.split("x"))
+        px, py = oracle.process_grid(int(p))
+        got = [list(oracle.decompose(m, n, px, py, r)) for r in range(int(p))]
+        assert got == blocks, key
+        # blocks tile the interior exactly once
+        cover = sum((b[1] - b[0] + 1) * (b[3] - b[2] + 1) for b in got)
+        assert cover == (m - 1) * (n - 1)
+
+
+@pytest.mark.parametrize("tag,m,n", [("full40", 40, 40), ("blk", 37, 53)])
+def test_setup_bit_exact(oracle, golden_arrays, tag, m, n):
+    a, b, B = oracle.setup(m, n)
+    for name, got in (("a", a), ("b", b), ("B", B)):
+        assert np.array_equal(got, golden_arrays[f"{name}_{tag}"]), name
+
+
+def test_setup_block_bit_exact(oracle, golden, golden_arrays):
+    blk = tuple(golden["block_400x600_rank5_of_8"])
+    a, b, B = oracle.setup(400, 600, blk)
+    assert np.array_equal(a[:24, :24], golden_arrays["a_blk5_win"])
+    assert np.array_equal(b[:24, :24], golden_arrays["b_blk5_win"])
+    chk = golden["block_checks"]
+    assert float(a.sum()) == chk["a_sum"] and float(b.sum()) == chk["b_sum"] and float(B.sum()) == chk["B_sum"]
+    assert float((a * a).sum()) == chk["a_sumsq"] and float((b * b).sum()) == chk["b_sumsq"]
+    # halo ring of B is zero, a/b are filled on it (S4:154-179, 182-191)
+    assert not B[0].any() and not B[-1].any() and not B[:, 0].any() and not B[:, -1].any()
+    assert a[0].all() and b[:, 0].all()
+
+
+def test_operators_bit_exact(oracle, golden, golden_arrays):
+    m = n = 40
+    h1, h2 = 2.0 / m, 1.2 / n
+    a, b = golden_arrays["a_full40"], golden_arrays["b_full40"]
+    p = seeded_field(m - 1, n - 1, seed=1234)
+    r = seeded_field(m - 1, n - 1, seed=4321)
+    assert np.array_equal(oracle.apply_A(p, a, b, h1, h2), golden_arrays["Ap_full40"])
+    assert np.array_equal(oracle.apply_Dinv(r, a, b, h1, h2), golden_arrays["z_full40"])
+    # summation order differs from the reference's OpenMP reduction: a few ulps
+    assert rel(oracle.dot(p, r, h1, h2), golden["dot_full40"]) < 1e-13
+    # z = r / D with the stored divisor
+    D = oracle.diag(a, b, h1, h2)
+    z = np.zeros_like(r)
+    z[1:-1, 1:-1] = r[1:-1, 1:-1] / D[1:-1, 1:-1]
+    assert np.array_equal(z, golden_arrays["z_full40"])
+
+
+def test_iteration_counts(oracle, golden):
+    for key, want in golden["iters_stage0"].items():
+        m, n = map(int, key.split("x"))
+        res, _, _ = oracle.solve(m, n, norm_mode=1)
+        assert res.iterations == want and res.converged, key
+    for key, want in golden["iters_stage3"].items():
+        m, n = map(int, key.split("x"))
+        if m * n > 400 * 600:
+            continue  # 800x1200 is covered by the slower test below
+        res, _, _ = oracle.solve(m, n)
+        assert res.iterations == want and res.converged, key
+
+
+@pytest.mark.parametrize("key", ["10x10", "20x20", "40x40", "400x600"])
+def test_solve_norms_and_trace(oracle, golden, golden_arrays, key):
+    m, n = map(int, key.split("x"))
+    g = golden["solves_stage3"][key]
+    tl = len(g["trace"])
+    res, w, trace = oracle.solve(m, n, want_w=True, trace_len=tl)
+    assert res.iterations == int(g["iterations"])
+    for f in ("w_norm_E", "w_max", "diff_norm", "zr", "alpha"):
+        assert rel(getattr(res, f), g[f]) < RTOL, (f, getattr(res, f), g[f])
+    gt = np.array(g["trace"])
+    np.testing.assert_allclose(trace, gt, rtol=1e-9, atol=0)
+    if key == "40x40":
+        np.testing.assert_allclose(w, golden_arrays["w_40x40"], rtol=0, atol=1e-13)
+        assert res.err_max_in_D == pytest.approx(6.418e-3, rel=2e-3)  # analytic-error sanity
+
+
+def test_solve_800x1200_iterations(oracle, golden):
+    res, _, _ = oracle.solve(800, 1200)
+    g = golden["solves_stage3"]["800x1200"]
+    assert res.iterations == golden["iters_stage3"]["800x1200"] == 989
+    # above 400x600 the reference's own summation-order spread is ~8e-10
+    assert rel(res.w_norm_E, g["w_norm_E"]) < 5e-9
+    assert rel(res.diff_norm, g["diff_norm"]) < 1e-9
+
+
+def test_block_solve_matches_single_rank(oracle, golden):
+    """P emulated ranks (decomposition + halo exchange) give the reference's multi-rank counts."""
+    for key, want in golden["iters_stage3_ranks"].items():
+        mn, p = key.split("@")
+        m, n = map(int, mn.split("x"))
+        if m * n > 40 * 60 and int(p) != 4:
+            continue
+        res, w = oracle.solve_blocks(m, n, int(p), want_w=True)
+        assert res.iterations == want, key
+        one, w1, _ = oracle.solve(m, n, want_w=True)
+        assert rel(res.w_norm_E, one.w_norm_E) < RTOL
+        np.testing.assert_allclose(w, w1, rtol=0, atol=1e-11)
+
+
+def test_fixed_iters_runs_past_convergence(oracle):
+    res, _, _ = oracle.solve(40, 40, fixed_iters=60)
+    assert res.iterations == 60 and not res.converged and res.diff_norm < 1e-6
+
+
+def test_against_live_reference(oracle, reference):
+    """When the reference itself is compiled here: operators bit-exact on a seeded odd-sized block."""
+    m, n = 53, 37
+    h1, h2 = 2.0 / m, 1.2 / n
+    px, py = reference.process_grid(6)
+    assert (px, py) == oracle.process_grid(6)
+    for rank in range(6):
+        blk = reference.decompose(m, n, px, py, rank)
+        assert blk == oracle.decompose(m, n, px, py, rank)
+        ra, rb, rB = reference.setup(m, n, blk)
+        a, b, B = oracle.setup(m, n, blk)
+        assert np.array_equal(a, ra) and np.array_equal(b, rb) and np.array_equal(B, rB)
+        nx, ny = a.shape[0] - 2, a.shape[1] - 2
+        p = seeded_field(nx, ny, seed=7 + rank)
+        assert np.array_equal(oracle.apply_A(p, a, b, h1, h2), reference.apply_A(p, a, b, h1, h2))
+        assert np.array_equal(oracle.apply_Dinv(p, a, b, h1, h2), reference.apply_Dinv(p, a, b, h1, h2))
+    assert oracle.solve(m, n)[0].iterations == reference.solve(m, n)
+    assert oracle.solve(m, n, norm_mode=1)[0].iterations == reference.solve_stage0(m, n)
