@@ -1,0 +1,191 @@
+// pb200_comm.cu -- multi-GPU plumbing: one rank per GPU, NCCL over NVLink/NVSwitch.
+//
+// Replaces the reference's host-staged MPI traffic (stage4-mpi+cuda/poisson_mpi_cuda_f.cu, "S4"):
+//   exchange_halos_2d_gpu (S4:331-500: 4 D2H copies, 4 MPI_Sendrecv, 4 H2D copies / memsets, all
+//   blocking)            -> one grouped ncclSend/ncclRecv between device buffers, on the solver stream;
+//   3 x MPI_Allreduce of one double per iteration (S4:872, 893, 926)
+//                        -> 2 x ncclAllReduce on the device-resident scalars (1 and 2 doubles).
+// What travels is the boundary of r (after K2), not of p: K1 recomputes p on the ring from r, D
+// and its own previous ring values, so one exchange per iteration suffices.
+//
+// NCCL is loaded with dlopen at first use: single-GPU users need no NCCL at all, and inside a
+// Python process that already imported torch the same libnccl.so.2 is shared.
+#include "pb200_solver.h"
+
+#include <cstring>
+#include <dlfcn.h>
+#include <mutex>
+#include <nccl.h>
+
+namespace pb200 {
+
+namespace {
+
+struct NcclApi {
+    void *handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    bool ok = false;
+};
+
+NcclApi &nccl() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        const char *names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char *n : names) {
+            api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+            if (api.handle) break;
+        }
+        if (!api.handle) return;
+        auto sym = [&](const char *s) { return dlsym(api.handle, s); };
+        api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(sym("ncclGetUniqueId"));
+        api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
+        api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
+        api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
+        api.Send = reinterpret_cast<decltype(api.Send)>(sym("ncclSend"));
+        api.Recv = reinterpret_cast<decltype(api.Recv)>(sym("ncclRecv"));
+        api.GroupStart = reinterpret_cast<decltype(api.GroupStart)>(sym("ncclGroupStart"));
+        api.GroupEnd = reinterpret_cast<decltype(api.GroupEnd)>(sym("ncclGroupEnd"));
+        api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+        api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllReduce && api.Send && api.Recv &&
+                 api.GroupStart && api.GroupEnd && api.GetErrorString;
+    });
+    return api;
+}
+
+#define NK(call)                                                                                      \
+    do {                                                                                              \
+        ncclResult_t r__ = (call);                                                                    \
+        if (r__ != ncclSuccess) {                                                                     \
+            ::pb200::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, nccl().GetErrorString(r__)); \
+            return PB200_ERR_COMM;                                                                    \
+        }                                                                                             \
+    } while (0)
+
+// column lj of r (rows 1..nx) <-> contiguous buffer
+__global__ void pack_cols_kernel(const double *__restrict__ r, int nx, int pitch, int ny, double *__restrict__ lo,
+                                 double *__restrict__ hi) {
+    const int li = 1 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (li > nx) return;
+    if (lo) lo[li - 1] = r[(size_t)li * pitch + 1];
+    if (hi) hi[li - 1] = r[(size_t)li * pitch + ny];
+}
+__global__ void unpack_cols_kernel(double *__restrict__ r, int nx, int pitch, int ny, const double *__restrict__ lo,
+                                   const double *__restrict__ hi) {
+    const int li = 1 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (li > nx) return;
+    if (lo) r[(size_t)li * pitch + 0] = lo[li - 1];
+    if (hi) r[(size_t)li * pitch + ny + 1] = hi[li - 1];
+}
+
+} // namespace
+
+struct Comm {
+    ncclComm_t nc = nullptr;
+    int left = -1, right = -1, down = -1, up = -1; // S4:341-344
+    double *send_lo = nullptr, *send_hi = nullptr, *recv_lo = nullptr, *recv_hi = nullptr; // packed columns
+    ncclResult_t async_err = ncclSuccess;
+};
+
+pb200_status comm_unique_id(uint8_t id_out[128]) {
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    if (!nccl().ok) { set_error("NCCL not available: dlopen(libnccl.so.2) failed"); return PB200_ERR_COMM; }
+    ncclUniqueId id;
+    NK(nccl().GetUniqueId(&id));
+    std::memcpy(id_out, &id, 128);
+    return PB200_OK;
+}
+
+pb200_status Solver::attach_comm(const uint8_t id_bytes[128]) {
+    if (prm.nranks <= 1) return PB200_OK;
+    if (!nccl().ok) { set_error("NCCL not available: dlopen(libnccl.so.2) failed"); return PB200_ERR_COMM; }
+    CK(cudaSetDevice(dev));
+    destroy_comm();
+    comm = new Comm();
+    ncclUniqueId id;
+    std::memcpy(&id, id_bytes, 128);
+    NK(nccl().CommInitRank(&comm->nc, prm.nranks, id, prm.rank));
+    const int px = prm.rank % Px, py = prm.rank / Px; // S4:338-344
+    comm->left = px > 0 ? prm.rank - 1 : -1;
+    comm->right = px < Px - 1 ? prm.rank + 1 : -1;
+    comm->down = py > 0 ? prm.rank - Px : -1;
+    comm->up = py < Py - 1 ? prm.rank + Px : -1;
+    const size_t nb = static_cast<size_t>(f.g.nx) * sizeof(double);
+    if (comm->down >= 0) { CK(cudaMalloc(&comm->send_lo, nb)); CK(cudaMalloc(&comm->recv_lo, nb)); }
+    if (comm->up >= 0) { CK(cudaMalloc(&comm->send_hi, nb)); CK(cudaMalloc(&comm->recv_hi, nb)); }
+    if (graph_exec) { cudaGraphExecDestroy(graph_exec); graph_exec = nullptr; }
+    return PB200_OK;
+}
+
+bool Solver::comm_ready() const { return comm && comm->nc; }
+
+void Solver::destroy_comm() {
+    if (!comm) return;
+    if (comm->nc && nccl().ok) nccl().CommDestroy(comm->nc);
+    for (double *q : {comm->send_lo, comm->send_hi, comm->recv_lo, comm->recv_hi})
+        if (q) cudaFree(q);
+    delete comm;
+    comm = nullptr;
+}
+
+void Solver::allreduce(int first, int count) {
+    ncclResult_t r = nccl().AllReduce(ctl->red + first, ctl->red + first, count, ncclDouble, ncclSum, comm->nc, stream);
+    if (r != ncclSuccess && comm->async_err == ncclSuccess) comm->async_err = r;
+}
+
+int Solver::halo_kernels_per_iteration() const {
+    return (comm && (comm->down >= 0 || comm->up >= 0)) ? 2 : 0;
+}
+
+void Solver::exchange_r_halo() {
+    const Geom &g = f.g;
+    const bool cols = comm->down >= 0 || comm->up >= 0;
+    const int tb = 256, nbk = (g.nx + tb - 1) / tb;
+    if (cols) pack_cols_kernel<<<nbk, tb, 0, stream>>>(f.r, g.nx, g.pitch, g.ny, comm->send_lo, comm->send_hi);
+    NcclApi &n = nccl();
+    ncclResult_t r = n.GroupStart();
+    auto acc = [&](ncclResult_t x) { if (x != ncclSuccess && r == ncclSuccess) r = x; };
+    const size_t P = g.pitch;
+    // i-direction neighbours share whole rows: contiguous, sent in place (interior cells lj = 1..ny)
+    if (comm->left >= 0) {
+        acc(n.Send(f.r + 1 * P + 1, g.ny, ncclDouble, comm->left, comm->nc, stream));
+        acc(n.Recv(f.r + 0 * P + 1, g.ny, ncclDouble, comm->left, comm->nc, stream));
+    }
+    if (comm->right >= 0) {
+        acc(n.Send(f.r + (size_t)g.nx * P + 1, g.ny, ncclDouble, comm->right, comm->nc, stream));
+        acc(n.Recv(f.r + (size_t)(g.nx + 1) * P + 1, g.ny, ncclDouble, comm->right, comm->nc, stream));
+    }
+    // j-direction neighbours share columns: packed
+    if (comm->down >= 0) {
+        acc(n.Send(comm->send_lo, g.nx, ncclDouble, comm->down, comm->nc, stream));
+        acc(n.Recv(comm->recv_lo, g.nx, ncclDouble, comm->down, comm->nc, stream));
+    }
+    if (comm->up >= 0) {
+        acc(n.Send(comm->send_hi, g.nx, ncclDouble, comm->up, comm->nc, stream));
+        acc(n.Recv(comm->recv_hi, g.nx, ncclDouble, comm->up, comm->nc, stream));
+    }
+    acc(n.GroupEnd());
+    if (r != ncclSuccess && comm->async_err == ncclSuccess) comm->async_err = r;
+    if (cols) unpack_cols_kernel<<<nbk, tb, 0, stream>>>(f.r, g.nx, g.pitch, g.ny, comm->recv_lo, comm->recv_hi);
+}
+
+pb200_status Solver::reduce_norms_host(double *) {
+    // in-stream: sums of w^2, r^2 and the max |w| (bit pattern of a non-negative double orders like uint64)
+    NK(nccl().AllReduce(norms, norms, 2, ncclDouble, ncclSum, comm->nc, stream));
+    NK(nccl().AllReduce(norms + 2, norms + 2, 1, ncclUint64, ncclMax, comm->nc, stream));
+    if (comm->async_err != ncclSuccess) {
+        set_error("NCCL error during the loop: %s", nccl().GetErrorString(comm->async_err));
+        return PB200_ERR_COMM;
+    }
+    return PB200_OK;
+}
+
+} // namespace pb200

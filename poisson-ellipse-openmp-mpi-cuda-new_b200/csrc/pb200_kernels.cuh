@@ -1,0 +1,584 @@
+// pb200_kernels.cuh -- device code of the fused PCG iteration for sm_100a.
+//
+// Replaces the seven kernels of the reference (stage4-mpi+cuda/poisson_mpi_cuda_f.cu, "S4"):
+//   setup_kernel  <- fictitious_regions_setup_local (host loop, S4:146-192) + zero_kernel (S4:599-609)
+//   k1_kernel     <- apply_Dinv_kernel (S4:541-562) + update_p_kernel (S4:663-676) / copy_kernel (S4:612-623)
+//                    + apply_A_kernel (S4:507-536) + dot_kernel for (Ap,p) (S4:574-598)
+//   k2_kernel     <- update_w_r_kernel (S4:626-660) + apply_Dinv_kernel + dot_kernel for (z,r)
+//                    + the host-side scalar logic of the loop (S4:872-906, 926-932)
+//
+// Arithmetic contract: every element-wise expression keeps the reference's expression tree with
+// one rounding per operation (this file is compiled with -fmad=false; the only fused operations
+// are the explicit __fma_rn inside div_const, which implements a correctly rounded division).
+//
+// Layout of a block (nx x ny interior cells, 1-cell ring): rows li = 0..nx+1, columns lj = 0..ny+1,
+// element (li,lj) at base[li*pitch + lj]; pitch is a multiple of 16 doubles so every row starts on
+// a 128-byte line; columns ny+2..pitch-1 are padding.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace pb200 {
+
+struct Geom {
+    int nx, ny;   // interior cells of this block
+    int pitch;    // doubles per row, multiple of 16
+    int gi0, gj0; // global index of local (0,0): i_start-1, j_start-1 (S4:156-157)
+    int M, N;
+};
+
+struct Consts {
+    double A1, A2;             // rectangle origin (S4:11-12)
+    double h1, h2;             // S4:691-692
+    double rh1, rh2;           // RN(1/h1), RN(1/h2) for div_const
+    double mih1, mih2;         // -1.0/h1, -1.0/h2 (S4:526, 530)
+    double h1h1, h2h2;         // h1*h1, h2*h2 (S4:556-557)
+    double eps, inv_eps;       // S4:693; 1.0/eps (S4:169)
+    double ell_k, ell_c;       // ellipse x^2 + (k y)^2 < 1; c = k*k (S4:33: 4.0)
+    double f_val;              // S4:13
+    double delta;              // S4:1006
+    int norm_mode;             // 0 weighted (S4:897), 1 stage0 (S0:154)
+    int fixed;                 // 1: delta test does not stop the loop
+    int multi;                 // 1: scalars are all-reduced between kernels, finalize runs separately
+    int trace_len;
+    long long max_iter;        // S4:1007 (or fixed_iters): enforced on the device
+};
+
+// Device-resident loop state: what the reference keeps in host variables (S4:836-848, 872-932).
+struct Ctl {
+    double zr_old;   // (z,r) of the previous iteration
+    double denom;    // (Ap,p)
+    double alpha, beta;
+    double diff;     // last ||w(k+1)-w(k)||
+    double red[4];   // [0] denom (this rank) [1] sum dw^2 (this rank, unweighted) [2] (z,r) (this rank) -- all-reduced in place when multi
+    long long iter;  // S4:848
+    int done;        // loop has ended; later kernels return immediately
+    int status;      // PB200_STOP_*
+    int conv_iter;   // first k with diff < delta
+    unsigned int ticket[2];
+};
+
+enum { STOP_MAX_ITER = 0, STOP_CONVERGED = 1, STOP_DENOM = 2 };
+
+// ------------------------------------------------------------------------------------------
+// small helpers
+
+__device__ __forceinline__ double dmax_std(double a, double b) { return (a < b) ? b : a; } // std::max
+__device__ __forceinline__ double dmin_std(double a, double b) { return (b < a) ? b : a; } // std::min
+
+// Correctly rounded x / h for a divisor h that is uniform over the grid, given rh = RN(1/h).
+// q0 = RN(x*rh) is within 1.5 ulp of x/h; one residual step makes it faithful (<= 0.5 ulp + 2^-53 ulp);
+// a second residual step on a faithful quotient with a correctly rounded reciprocal yields RN(x/h)
+// (Markstein's theorem). Both residuals x - h*q are exact in an FMA. Outside the range where the
+// residuals stay normal (and for NaN/Inf) the IEEE divide is used. pb200_selftest_div checks this
+// against x/h on the device. 5 FP64 ops instead of the ~10 + MUFU + branch of the generic divide,
+// of which the stencil needs four per point (S4:527-532).
+__device__ __forceinline__ double div_const(double x, double h, double rh) {
+    double q = __dmul_rn(x, rh);
+    double e = __fma_rn(-h, q, x);
+    q = __fma_rn(e, rh, q);
+    e = __fma_rn(-h, q, x);
+    q = __fma_rn(e, rh, q);
+    const double ax = fabs(x);
+    if (!((ax > 0x1p-900 && ax < 0x1p900) || ax == 0.0)) q = __ddiv_rn(x, h);
+    return q;
+}
+
+__device__ __forceinline__ double2 ld2(const double *__restrict__ base, size_t off, bool ok) {
+    double2 v = make_double2(0.0, 0.0);
+    if (ok) v = __ldg(reinterpret_cast<const double2 *>(base + off));
+    return v;
+}
+
+__device__ __forceinline__ double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
+__device__ __forceinline__ double shfl_dn1(double v) { return __shfl_down_sync(0xffffffffu, v, 1); }
+
+// Fixed-shape warp sum: lane 0 ends with ((..(v0+v16)+(v8+v24)..)) -- same tree every run.
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Block-level deterministic reduction of up to NV values per thread, followed by the
+// "last block sums all block partials in index order" pass. Returns true in thread 0 of the
+// last block with the grid totals in out[0..NV). partials: [NV][nblocks].
+template <int NV, int THREADS>
+__device__ __forceinline__ bool grid_reduce(double (&v)[NV], double *partials, unsigned int *ticket, double (&out)[NV]) {
+    __shared__ double s_w[NV][THREADS / 32];
+    __shared__ bool s_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned nblocks = gridDim.x * gridDim.y;
+    const unsigned bid = blockIdx.y * gridDim.x + blockIdx.x;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        double w = warp_sum(v[k]);
+        if (lane == 0) s_w[k][warp] = w;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) {
+            double s = 0.0;
+#pragma unroll
+            for (int w = 0; w < THREADS / 32; ++w) s += s_w[k][w];
+            __stcg(&partials[(size_t)k * nblocks + bid], s);
+        }
+        __threadfence();
+        unsigned t = atomicAdd(ticket, 1u);
+        s_last = (t == nblocks - 1);
+    }
+    __syncthreads();
+    if (!s_last) return false;
+    __threadfence();
+    // last block: thread t sums partials t, t+THREADS, ... in order; then the fixed tree above.
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        double s = 0.0;
+        for (unsigned i = threadIdx.x; i < nblocks; i += THREADS) s += __ldcg(&partials[(size_t)k * nblocks + i]);
+        double w = warp_sum(s);
+        if (lane == 0) s_w[k][warp] = w;
+    }
+    __syncthreads();
+    if (threadIdx.x != 0) return false;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < THREADS / 32; ++w) s += s_w[k][w];
+        out[k] = s;
+    }
+    *ticket = 0u; // ready for the next launch
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------
+// geometry (S4:32-76, 159-177). Expression trees follow the reference exactly.
+
+__device__ __forceinline__ double seg_len(const Consts &c, double cc, double s, double e, bool vertical) {
+    double l;
+    if (vertical) {
+        const double x0 = cc;
+        if (fabs(x0) >= 1.0) l = 0.0; // S4:51
+        else {
+            const double root = sqrt(dmax_std(0.0, (1.0 - x0 * x0) / c.ell_c)); // S4:53-54
+            l = dmax_std(0.0, dmin_std(e, root) - dmax_std(s, -root));          // S4:55
+        }
+    } else {
+        const double y0 = cc;
+        if (fabs(c.ell_k * y0) >= 1.0) l = 0.0; // S4:59
+        else {
+            const double root = sqrt(dmax_std(0.0, 1.0 - c.ell_c * y0 * y0)); // S4:61-62
+            l = dmax_std(0.0, dmin_std(e, root) - dmax_std(s, -root));        // S4:63
+        }
+    }
+    return l;
+}
+
+__device__ __forceinline__ double coef_a(const Consts &c, int gi, int gj) { // S4:159-163, 167-171
+    const double x = c.A1 + gi * c.h1, y = c.A2 + gj * c.h2;
+    const double l = seg_len(c, x - 0.5 * c.h1, y - 0.5 * c.h2, y + 0.5 * c.h2, true);
+    return (fabs(l - c.h2) < 1e-9) ? 1.0 : (l < 1e-9 ? 1.0 / c.eps : (l / c.h2) + (1.0 - l / c.h2) / c.eps);
+}
+__device__ __forceinline__ double coef_b(const Consts &c, int gi, int gj) { // S4:159-160, 164-165, 173-177
+    const double x = c.A1 + gi * c.h1, y = c.A2 + gj * c.h2;
+    const double l = seg_len(c, y - 0.5 * c.h2, x - 0.5 * c.h1, x + 0.5 * c.h1, false);
+    return (fabs(l - c.h1) < 1e-9) ? 1.0 : (l < 1e-9 ? 1.0 / c.eps : (l / c.h1) + (1.0 - l / c.h1) / c.eps);
+}
+
+// One thread per stored cell (ring and padding included). Writes a, b (block + ring, S4:154-179),
+// r = B (S4:182-191, 813) on every cell that is a global interior node -- ring cells owned by a
+// neighbour block get the neighbour's values, so no halo exchange is needed before iteration 1 --
+// D (S4:556-557) likewise, and w = p = p' = Ap = 0 (S4:805; zero ring = Dirichlet condition S4:444-492).
+__global__ void __launch_bounds__(256) setup_kernel(Geom g, Consts c, double *__restrict__ a, double *__restrict__ b,
+                                                    double *__restrict__ D, double *__restrict__ r,
+                                                    double *__restrict__ w, double *__restrict__ p0,
+                                                    double *__restrict__ p1, double *__restrict__ Ap) {
+    const int lj = blockIdx.x * blockDim.x + threadIdx.x;
+    const int li = blockIdx.y;
+    if (lj >= g.pitch) return;
+    const size_t o = (size_t)li * g.pitch + lj;
+    double va = 0.0, vb = 0.0, vD = 1.0, vr = 0.0;
+    if (lj <= g.ny + 1) {
+        const int gi = g.gi0 + li, gj = g.gj0 + lj;
+        va = coef_a(c, gi, gj);
+        vb = coef_b(c, gi, gj);
+        if (gi >= 1 && gi <= g.M - 1 && gj >= 1 && gj <= g.N - 1) {
+            const double x = c.A1 + gi * c.h1, y = c.A2 + gj * c.h2;
+            vr = (x * x + c.ell_c * y * y < 1.0) ? c.f_val : 0.0; // S4:32-34, 189
+            vD = (coef_a(c, gi + 1, gj) + va) / c.h1h1 + (coef_b(c, gi, gj + 1) + vb) / c.h2h2; // S4:556-557
+        }
+    }
+    a[o] = va;
+    b[o] = vb;
+    D[o] = vD;
+    r[o] = vr;
+    if (w) w[o] = 0.0;
+    if (p0) p0[o] = 0.0;
+    if (p1) p1[o] = 0.0;
+    if (Ap) Ap[o] = 0.0;
+}
+
+// D from caller-supplied a, b (operator entry points only: the solver's D comes from setup_kernel).
+__global__ void __launch_bounds__(256) diag_kernel(Geom g, Consts c, const double *__restrict__ a,
+                                                   const double *__restrict__ b, double *__restrict__ D) {
+    const int lj = blockIdx.x * blockDim.x + threadIdx.x;
+    const int li = blockIdx.y;
+    if (lj >= g.pitch) return;
+    const size_t o = (size_t)li * g.pitch + lj;
+    double vD = 1.0;
+    if (li >= 1 && li <= g.nx && lj >= 1 && lj <= g.ny)
+        vD = (a[o + g.pitch] + a[o]) / c.h1h1 + (b[o + 1] + b[o]) / c.h2h2;
+    D[o] = vD;
+}
+
+// ------------------------------------------------------------------------------------------
+// K1: p' = D^-1 r + beta p ; Ap = A p' ; partial (Ap,p').
+//
+// A warp owns 62 adjacent columns and marches down a segment of rows. Lane l holds columns
+// s+2l, s+2l+1 of a 64-column window [s, s+64), s = 62*warp_column: the window's first and last
+// column are the left/right neighbours of the owned range, recomputed instead of exchanged, so
+// warps never synchronise with each other. p' of rows i-1, i, i+1 lives in registers; each new
+// row costs one 16-byte load per lane from r, D, p, a, b and one 16-byte store to p', Ap.
+// The operands of row i+2 are requested before row i is computed.
+
+constexpr int K1_WARPS = 8;
+constexpr int K1_THREADS = K1_WARPS * 32;
+constexpr int K1_OWN = 62; // owned columns per warp
+
+struct K1Args {
+    const double *r, *D, *p_old, *a, *b;
+    double *p_new, *Ap;
+    double *partials; // [nblocks]
+    Ctl *ctl;
+    Geom g;
+    Consts c;
+    int rows_per_seg;
+};
+
+struct RowIn {
+    double2 r, D, q, a; // row n = i+1
+    double2 b;          // row i
+};
+
+template <bool FIRST>
+__device__ __forceinline__ double2 p_update(const double2 r, const double2 D, const double2 q, const double beta) {
+    double2 z, o;
+    z.x = (D.x != 0.0) ? r.x / D.x : 0.0; // S4:559
+    z.y = (D.y != 0.0) ? r.y / D.y : 0.0;
+    if (FIRST) return z;                  // S4:830: p = z
+    o.x = z.x + beta * q.x;               // S4:675
+    o.y = z.y + beta * q.y;
+    return o;
+}
+
+template <bool FIRST>
+__global__ void __launch_bounds__(K1_THREADS) k1_kernel(const K1Args A) {
+    Ctl *ctl = A.ctl;
+    if (*reinterpret_cast<volatile int *>(&ctl->done)) return;
+    const Geom g = A.g;
+    const double h1 = A.c.h1, h2 = A.c.h2, rh1 = A.c.rh1, rh2 = A.c.rh2, mih1 = A.c.mih1, mih2 = A.c.mih2;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int s = (blockIdx.x * K1_WARPS + warp) * K1_OWN;
+    const int c0 = s + 2 * lane;
+    const int i_lo = 1 + blockIdx.y * A.rows_per_seg;
+    const int i_hi = min(g.nx, i_lo + A.rows_per_seg - 1);
+    const double beta = FIRST ? 0.0 : ctl->beta;
+
+    double acc[1] = {0.0};
+    if (s + 1 <= g.ny) { // warp-uniform: this warp owns at least one interior column
+        const bool ld_ok = (c0 + 1 < g.pitch);
+        // stencil outputs: owned columns that are interior cells
+        const bool own_x = (lane > 0) && (c0 <= g.ny);
+        const bool own_y = (lane < 31) && (c0 + 1 <= g.ny);
+        // p' is also kept up to date on the ring (it is the neighbour block's boundary value)
+        const bool wr_x = (c0 <= g.ny + 1) && (lane > 0 || s == 0);
+        const bool wr_y = (c0 + 1 <= g.ny + 1) && (lane < 31 || c0 + 1 == g.ny + 1);
+        const size_t P = (size_t)g.pitch;
+
+        auto store2 = [&](double *base, size_t off, double2 v, bool x, bool y) {
+            if (x && y) *reinterpret_cast<double2 *>(base + off) = v;
+            else if (x) base[off] = v.x;
+            else if (y) base[off + 1] = v.y;
+        };
+        auto load_row = [&](int n, bool with_b) {
+            RowIn in;
+            const size_t o = (size_t)n * P + c0;
+            in.r = ld2(A.r, o, ld_ok);
+            in.D = ld2(A.D, o, ld_ok);
+            in.q = FIRST ? make_double2(0.0, 0.0) : ld2(A.p_old, o, ld_ok);
+            in.a = ld2(A.a, o, ld_ok);
+            in.b = with_b ? ld2(A.b, o - P, ld_ok) : make_double2(0.0, 0.0);
+            return in;
+        };
+
+        // rows i_lo-1 and i_lo
+        RowIn in = load_row(i_lo - 1, false);
+        double2 pm = p_update<FIRST>(in.r, in.D, in.q, beta);
+        if (i_lo == 1) store2(A.p_new, (size_t)0 * P + c0, pm, wr_x, wr_y); // ring row 0
+        in = load_row(i_lo, false);
+        double2 pc = p_update<FIRST>(in.r, in.D, in.q, beta);
+        double2 ac = in.a;
+        store2(A.p_new, (size_t)i_lo * P + c0, pc, wr_x, wr_y);
+
+        RowIn nxt = load_row(i_lo + 1, true);
+        for (int i = i_lo; i <= i_hi; ++i) {
+            const RowIn cur = nxt;
+            if (i < i_hi) nxt = load_row(i + 2, true); // in flight while row i is computed
+            const double2 pn = p_update<FIRST>(cur.r, cur.D, cur.q, beta);
+            const double2 an = cur.a, bc = cur.b;
+            if (i + 1 <= i_hi || i + 1 == g.nx + 1) store2(A.p_new, (size_t)(i + 1) * P + c0, pn, wr_x, wr_y);
+
+            // j-neighbours: left of .x is the previous lane's .y, right of .y is the next lane's .x
+            const double pl = shfl_up1(pc.y);
+            const double pr = shfl_dn1(pc.x);
+            const double br = shfl_dn1(bc.x);
+            double2 out;
+            {   // S4:526-535 for column c0
+                const double ax = mih1 * (div_const(an.x * (pn.x - pc.x), h1, rh1) - div_const(ac.x * (pc.x - pm.x), h1, rh1));
+                const double ay = mih2 * (div_const(bc.y * (pc.y - pc.x), h2, rh2) - div_const(bc.x * (pc.x - pl), h2, rh2));
+                out.x = ax + ay;
+            }
+            {   // column c0+1
+                const double ax = mih1 * (div_const(an.y * (pn.y - pc.y), h1, rh1) - div_const(ac.y * (pc.y - pm.y), h1, rh1));
+                const double ay = mih2 * (div_const(br * (pr - pc.y), h2, rh2) - div_const(bc.y * (pc.y - pc.x), h2, rh2));
+                out.y = ax + ay;
+            }
+            store2(A.Ap, (size_t)i * P + c0, out, own_x, own_y);
+            if (own_x) acc[0] += out.x * pc.x; // S4:594: sum += x*y
+            if (own_y) acc[0] += out.y * pc.y;
+            pm = pc;
+            pc = pn;
+            ac = an;
+        }
+    }
+
+    double tot[1];
+    if (grid_reduce<1, K1_THREADS>(acc, A.partials, &ctl->ticket[0], tot)) {
+        ctl->red[0] = tot[0] * h1 * h2; // S3:191: sum * h1 * h2
+        ctl->iter = ctl->iter + 1;      // S4:847-848: k
+        if (!A.c.multi) ctl->denom = ctl->red[0];
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K2: alpha = zr_old/denom ; w += alpha p' ; r -= alpha Ap ; sum dw^2 ; z = D^-1 r ; sum z r ;
+// then (single GPU) the scalar tail of the iteration: stopping test, beta, zr_old.
+
+constexpr int K2_THREADS = 256;
+constexpr int K2_ROWS = 4; // rows per thread
+
+struct K2Args {
+    double *w, *r;
+    const double *p, *Ap, *D;
+    double *partials; // [2][nblocks]
+    double *trace;    // [trace_len][3] or null
+    Ctl *ctl;
+    Geom g;
+    Consts c;
+};
+
+// The scalar tail of one iteration (S4:893-906, 926-932), run by exactly one thread.
+__device__ __forceinline__ void finalize_iteration(Ctl *ctl, const Consts &c, double *trace, double alpha, double diff2,
+                                                   double zr_new) {
+    const long long k = ctl->iter;
+    const double diff = (c.norm_mode == 0) ? sqrt(diff2 * c.h1 * c.h2) : sqrt(diff2); // S3:449 | S0:154
+    ctl->diff = diff;
+    ctl->alpha = alpha;
+    const bool conv = diff < c.delta; // S4:899
+    if (trace && k <= c.trace_len) {
+        trace[3 * (k - 1) + 0] = alpha;
+        trace[3 * (k - 1) + 1] = 0.0;
+        trace[3 * (k - 1) + 2] = diff;
+    }
+    if (conv && ctl->conv_iter == 0) ctl->conv_iter = (int)k;
+    if (conv && !c.fixed) {
+        ctl->status = STOP_CONVERGED;
+        __threadfence();
+        ctl->done = 1;
+        return;
+    }
+    const double beta = zr_new / ctl->zr_old; // S4:931
+    ctl->beta = beta;
+    ctl->zr_old = zr_new; // S4:932
+    if (trace && k <= c.trace_len) trace[3 * (k - 1) + 1] = beta;
+    if (k >= c.max_iter) { // S4:847: loop bound
+        ctl->status = STOP_MAX_ITER;
+        __threadfence();
+        ctl->done = 1;
+    }
+}
+
+// MODE 0: iteration. MODE 1: initialisation -- only zr_old = (D^-1 r, r) (S4:820-843); w, r untouched.
+template <int MODE>
+__global__ void __launch_bounds__(K2_THREADS) k2_kernel(const K2Args A) {
+    Ctl *ctl = A.ctl;
+    if (*reinterpret_cast<volatile int *>(&ctl->done)) return;
+    const Geom g = A.g;
+    double alpha = 0.0;
+    if (MODE == 0) {
+        const double denom = A.c.multi ? ctl->red[0] : ctl->denom;
+        const bool brk = (A.c.norm_mode == 1) ? (denom < 1e-15) : (fabs(denom) < 1e-15); // S0:128 | S4:876
+        if (brk) {
+            if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
+                ctl->denom = denom;
+                ctl->status = STOP_DENOM;
+                __threadfence();
+                ctl->done = 1;
+            }
+            return;
+        }
+        alpha = ctl->zr_old / denom; // S4:877
+    }
+    const int c0 = 2 * (blockIdx.x * K2_THREADS + threadIdx.x);
+    const int li0 = 1 + blockIdx.y * K2_ROWS;
+    const bool vx = (c0 >= 1) && (c0 <= g.ny);
+    const bool vy = (c0 + 1 <= g.ny);
+    double acc[2] = {0.0, 0.0};
+    if (vx || vy) {
+        double2 w[K2_ROWS], r[K2_ROWS], p[K2_ROWS], q[K2_ROWS], D[K2_ROWS];
+#pragma unroll
+        for (int t = 0; t < K2_ROWS; ++t) {
+            const int li = li0 + t;
+            const bool ok = li <= g.nx;
+            const size_t o = (size_t)li * g.pitch + c0;
+            r[t] = ld2(A.r, o, ok);
+            D[t] = ok ? __ldg(reinterpret_cast<const double2 *>(A.D + o)) : make_double2(1.0, 1.0);
+            if (MODE == 0) {
+                w[t] = ld2(A.w, o, ok);
+                p[t] = ld2(A.p, o, ok);
+                q[t] = ld2(A.Ap, o, ok);
+            }
+        }
+#pragma unroll
+        for (int t = 0; t < K2_ROWS; ++t) {
+            const int li = li0 + t;
+            if (li > g.nx) break;
+            const size_t o = (size_t)li * g.pitch + c0;
+            double2 wn = make_double2(0.0, 0.0), rn = r[t];
+            if (MODE == 0) {
+                wn.x = w[t].x + alpha * p[t].x; // S4:647
+                wn.y = w[t].y + alpha * p[t].y;
+                rn.x = r[t].x - alpha * q[t].x; // S4:648
+                rn.y = r[t].y - alpha * q[t].y;
+                const double dx = wn.x - w[t].x, dy = wn.y - w[t].y; // S4:653
+                if (vx) acc[0] += dx * dx;
+                if (vy) acc[0] += dy * dy;
+                if (vx && vy) {
+                    *reinterpret_cast<double2 *>(A.w + o) = wn;
+                    *reinterpret_cast<double2 *>(A.r + o) = rn;
+                } else if (vx) {
+                    A.w[o] = wn.x;
+                    A.r[o] = rn.x;
+                } else {
+                    A.w[o + 1] = wn.y;
+                    A.r[o + 1] = rn.y;
+                }
+            }
+            const double zx = (D[t].x != 0.0) ? rn.x / D[t].x : 0.0; // S4:559
+            const double zy = (D[t].y != 0.0) ? rn.y / D[t].y : 0.0;
+            if (vx) acc[1] += zx * rn.x; // S4:594
+            if (vy) acc[1] += zy * rn.y;
+        }
+    }
+    double tot[2];
+    if (grid_reduce<2, K2_THREADS>(acc, A.partials, &ctl->ticket[1], tot)) {
+        const double zr = tot[1] * A.c.h1 * A.c.h2; // S3:191
+        ctl->red[1] = tot[0];
+        ctl->red[2] = zr;
+        if (!A.c.multi) {
+            if (MODE == 1) ctl->zr_old = zr; // S4:838-843
+            else finalize_iteration(ctl, A.c, A.trace, alpha, tot[0], zr);
+        }
+    }
+}
+
+// Multi-GPU: after the all-reduce of red[1..2] (or red[2] at init) every rank runs the same scalar tail.
+__global__ void finalize_kernel(Ctl *ctl, Consts c, double *trace, int init) {
+    if (*reinterpret_cast<volatile int *>(&ctl->done)) return;
+    if (init) {
+        ctl->zr_old = ctl->red[2];
+        return;
+    }
+    const double denom = ctl->red[0];
+    ctl->denom = denom;
+    finalize_iteration(ctl, c, trace, ctl->zr_old / denom, ctl->red[1], ctl->red[2]);
+}
+
+// ------------------------------------------------------------------------------------------
+// norms of the result (reporting only): sum w^2, sum r^2, max |w| over the interior.
+__global__ void __launch_bounds__(256) norms_kernel(Geom g, const double *__restrict__ w, const double *__restrict__ r,
+                                                    double *partials, unsigned int *ticket, double *out3) {
+    double acc[2] = {0.0, 0.0};
+    double mx = 0.0;
+    const int lj = 1 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (lj <= g.ny)
+        for (int li = 1 + blockIdx.y; li <= g.nx; li += gridDim.y) {
+            const size_t o = (size_t)li * g.pitch + lj;
+            const double vw = w[o], vr = r[o];
+            acc[0] += vw * vw;
+            acc[1] += vr * vr;
+            mx = fmax(mx, fabs(vw));
+        }
+    // max via ordered-int atomics on the bit pattern (non-negative doubles order like integers)
+    atomicMax(reinterpret_cast<unsigned long long *>(&out3[2]), (unsigned long long)__double_as_longlong(mx));
+    double tot[2];
+    if (grid_reduce<2, 256>(acc, partials, ticket, tot)) {
+        out3[0] = tot[0];
+        out3[1] = tot[1];
+    }
+}
+
+// Generic weighted inner product (operator entry point; the solver's dots are fused into K1/K2).
+__global__ void __launch_bounds__(256) dot_kernel(Geom g, const double *__restrict__ u, const double *__restrict__ v,
+                                                  double *partials, unsigned int *ticket, double *out) {
+    double acc[1] = {0.0};
+    const int lj = 1 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (lj <= g.ny)
+        for (int li = 1 + blockIdx.y; li <= g.nx; li += gridDim.y) {
+            const size_t o = (size_t)li * g.pitch + lj;
+            acc[0] += u[o] * v[o];
+        }
+    double tot[1];
+    if (grid_reduce<1, 256>(acc, partials, ticket, tot)) out[0] = tot[0];
+}
+
+// ------------------------------------------------------------------------------------------
+// self-test of div_const against the IEEE divide.
+__global__ void selftest_div_kernel(double h, double rh, long long n, unsigned long long seed,
+                                    unsigned long long *mismatches) {
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    unsigned long long bad = 0;
+    for (long long i = tid; i < n; i += stride) {
+        unsigned long long z = seed + 0x9E3779B97F4A7C15ull * (unsigned long long)(i + 1);
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        // (1) random mantissa, exponent in [-40, 40]
+        const int ex = (int)((z >> 52) % 81) - 40;
+        double x = ldexp(1.0 + (double)(z & ((1ull << 52) - 1)) * 0x1p-52, ex);
+        if (z >> 63) x = -x;
+        if (__double_as_longlong(div_const(x, h, rh)) != __double_as_longlong(__ddiv_rn(x, h))) ++bad;
+        // (2) adversarial: x next to h*m, so that x/h sits next to a representable value or a midpoint
+        const double m = 1.0 + (double)((z >> 7) & ((1ull << 52) - 1)) * 0x1p-52;
+        const double hm = __dmul_rn(h, m);
+        const long long bits = __double_as_longlong(hm);
+#pragma unroll
+        for (int d = -2; d <= 2; ++d) {
+            const double xa = __longlong_as_double(bits + d);
+            if (__double_as_longlong(div_const(xa, h, rh)) != __double_as_longlong(__ddiv_rn(xa, h))) ++bad;
+        }
+        // (3) x/h near a midpoint: x = h*(m + half an ulp) rounded either way
+        const double mh = __fma_rn(h, m, __dmul_rn(h, 0x1p-53));
+        const long long b2 = __double_as_longlong(mh);
+#pragma unroll
+        for (int d = -1; d <= 1; ++d) {
+            const double xa = __longlong_as_double(b2 + d);
+            if (__double_as_longlong(div_const(xa, h, rh)) != __double_as_longlong(__ddiv_rn(xa, h))) ++bad;
+        }
+    }
+    if (bad) atomicAdd(mismatches, bad);
+}
+
+} // namespace pb200

@@ -1,0 +1,403 @@
+// pb200_solver.cu -- host side of libpoisson_b200.so: the solver object behind the C ABI of
+// include/poisson_b200.h. Replaces gradient_solver_mpi (stage4-mpi+cuda/poisson_mpi_cuda_f.cu,
+// "S4", lines 688-983) and the parts of main that feed it (S4:996-1007).
+//
+// Differences in structure from the reference (by design):
+//   * coefficients, RHS and preconditioner diagonal are computed by a kernel, not on the host
+//     (S4:717 + 723-760);
+//   * one iteration is two kernels with the scalar logic on the device; the host never waits for
+//     a scalar (the reference blocks ~20 times per iteration). The host only polls
+//     a device-side stop flag every `check_every` iterations, one batch behind the GPU;
+//   * the iteration is replayed as a CUDA graph (two iterations per graph: p ping-pongs).
+#include "pb200_solver.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+namespace pb200 {
+
+thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+static double now_s() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// S4:82-86
+void choose_process_grid(int size, int &Px, int &Py) {
+    Px = static_cast<int>(std::sqrt(static_cast<double>(size)));
+    while (Px > 1 && size % Px != 0) --Px;
+    Py = size / Px;
+}
+
+// S4:97-133
+void decompose_2d(int M, int N, int Px, int Py, int rank, int &i0, int &i1, int &j0, int &j1) {
+    const int px = rank % Px, py = rank / Px;
+    auto split = [](int total, int parts, int coord, int &lo, int &hi) {
+        const int base = total / parts, rem = total % parts;
+        lo = 1 + coord * base + std::min(coord, rem); // 1 + sum_{k<coord} (base + (k<rem))
+        hi = lo + base + (coord < rem ? 1 : 0) - 1;
+    };
+    split(M - 1, Px, px, i0, i1);
+    split(N - 1, Py, py, j0, j1);
+}
+
+pb200_status validate(const pb200_params &p) {
+    if (p.M < 2 || p.N < 2) { set_error("M and N must be >= 2 (got %d, %d)", p.M, p.N); return PB200_ERR_INVALID; }
+    if (!(p.B1 > p.A1) || !(p.B2 > p.A2)) { set_error("empty rectangle"); return PB200_ERR_INVALID; }
+    if (!(p.ell_k > 0.0)) { set_error("ell_k must be > 0"); return PB200_ERR_INVALID; }
+    if (!(p.delta >= 0.0)) { set_error("delta must be >= 0"); return PB200_ERR_INVALID; }
+    if (p.norm_mode != PB200_NORM_WEIGHTED && p.norm_mode != PB200_NORM_STAGE0) { set_error("bad norm_mode"); return PB200_ERR_INVALID; }
+    if (p.nranks < 1 || p.rank < 0 || p.rank >= p.nranks) { set_error("bad rank %d of %d", p.rank, p.nranks); return PB200_ERR_INVALID; }
+    if (p.Px > 0 && p.Py > 0 && p.Px * p.Py != p.nranks) { set_error("Px*Py != nranks"); return PB200_ERR_INVALID; }
+    const double h1 = (p.B1 - p.A1) / p.M, h2 = (p.B2 - p.A2) / p.N;
+    if (!(h1 > 0x1p-100 && h1 < 0x1p100 && h2 > 0x1p-100 && h2 < 0x1p100)) { set_error("grid step out of range"); return PB200_ERR_INVALID; }
+    return PB200_OK;
+}
+
+Consts make_consts(const pb200_params &p) {
+    Consts c{};
+    c.A1 = p.A1;
+    c.A2 = p.A2;
+    c.h1 = (p.B1 - p.A1) / p.M; // S4:691
+    c.h2 = (p.B2 - p.A2) / p.N; // S4:692
+    c.rh1 = 1.0 / c.h1;
+    c.rh2 = 1.0 / c.h2;
+    c.mih1 = -1.0 / c.h1; // S4:526
+    c.mih2 = -1.0 / c.h2; // S4:530
+    c.h1h1 = c.h1 * c.h1; // S4:556
+    c.h2h2 = c.h2 * c.h2; // S4:557
+    c.eps = p.eps > 0.0 ? p.eps : std::max(c.h1, c.h2) * std::max(c.h1, c.h2); // S4:693
+    c.inv_eps = 1.0 / c.eps;
+    c.ell_k = p.ell_k;
+    c.ell_c = p.ell_k * p.ell_k;
+    c.f_val = p.f_val;
+    c.delta = p.delta;
+    c.norm_mode = p.norm_mode;
+    c.fixed = p.fixed_iters > 0;
+    c.multi = p.nranks > 1;
+    c.trace_len = std::max(0, p.trace_len);
+    const long long dflt = static_cast<long long>(p.M - 1) * static_cast<long long>(p.N - 1); // S4:1007
+    c.max_iter = p.fixed_iters > 0 ? p.fixed_iters : (p.max_iter > 0 ? p.max_iter : dflt);
+    return c;
+}
+
+int pitch_for(int ny) { return ((ny + 2 + 15) / 16) * 16; }
+
+// ---------------------------------------------------------------------------------------------
+
+Fields::~Fields() { release(); }
+
+void Fields::release() {
+    double **all[] = {&a, &b, &D, &w, &r, &p[0], &p[1], &Ap};
+    for (double **q : all) {
+        if (*q) cudaFree(*q);
+        *q = nullptr;
+    }
+}
+
+pb200_status Fields::allocate(const Geom &geom) {
+    g = geom;
+    elems = static_cast<size_t>(g.nx + 2) * static_cast<size_t>(g.pitch);
+    double **all[] = {&a, &b, &D, &w, &r, &p[0], &p[1], &Ap};
+    for (double **q : all) CK(cudaMalloc(q, elems * sizeof(double)));
+    return PB200_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+
+Solver::~Solver() {
+    if (dev >= 0) cudaSetDevice(dev);
+    destroy_comm();
+    if (graph_exec) cudaGraphExecDestroy(graph_exec);
+    for (auto &e : ev_poll) if (e) cudaEventDestroy(e);
+    if (ev_start) cudaEventDestroy(ev_start);
+    if (ev_stop) cudaEventDestroy(ev_stop);
+    if (ctl) cudaFree(ctl);
+    if (part1) cudaFree(part1);
+    if (part2) cudaFree(part2);
+    if (trace) cudaFree(trace);
+    if (norms) cudaFree(norms);
+    if (h_ctl) cudaFreeHost(h_ctl);
+    f.release();
+    if (stream) cudaStreamDestroy(stream);
+}
+
+void Solver::plan_launch() {
+    // K1: warps own 62 columns; rows are cut into segments so that the grid has several waves.
+    const int wcols = (f.g.ny + K1_OWN - 1) / K1_OWN;
+    k1_grid.x = (wcols + K1_WARPS - 1) / K1_WARPS;
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // aim for >= 6 CTAs per SM in total, segments between 8 and 64 rows
+    const long long want = 6LL * sms;
+    int segs = static_cast<int>((want + k1_grid.x - 1) / k1_grid.x);
+    int rows = (f.g.nx + segs - 1) / std::max(1, segs);
+    rows = std::max(8, std::min(64, rows));
+    rows_per_seg = rows;
+    k1_grid.y = (f.g.nx + rows - 1) / rows;
+    k1_grid.z = 1;
+    const int cols2 = f.g.ny / 2 + 1; // threads needed: columns 0..ny in pairs
+    k2_grid.x = (cols2 + K2_THREADS - 1) / K2_THREADS;
+    k2_grid.y = (f.g.nx + K2_ROWS - 1) / K2_ROWS;
+    k2_grid.z = 1;
+    norms_grid = dim3((f.g.ny + 255) / 256, std::min(f.g.nx, 512), 1);
+}
+
+pb200_status Solver::create(const pb200_params &params) {
+    const double t0 = now_s();
+    prm = params;
+    pb200_status st = validate(prm);
+    if (st != PB200_OK) return st;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        set_error("no CUDA device: libpoisson_b200 has no CPU path");
+        return PB200_ERR_CUDA;
+    }
+    if (prm.device >= 0) CK(cudaSetDevice(prm.device));
+    CK(cudaGetDevice(&dev));
+    Px = prm.Px;
+    Py = prm.Py;
+    if (Px <= 0 || Py <= 0) choose_process_grid(prm.nranks, Px, Py);
+    if (Px > prm.M - 1 || Py > prm.N - 1) { set_error("more blocks than interior nodes"); return PB200_ERR_INVALID; }
+    decompose_2d(prm.M, prm.N, Px, Py, prm.rank, i0, i1, j0, j1);
+    Geom g{};
+    g.nx = i1 - i0 + 1;
+    g.ny = j1 - j0 + 1;
+    g.pitch = pitch_for(g.ny);
+    g.gi0 = i0 - 1;
+    g.gj0 = j0 - 1;
+    g.M = prm.M;
+    g.N = prm.N;
+    c = make_consts(prm);
+    CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    st = f.allocate(g);
+    if (st != PB200_OK) return st;
+    plan_launch();
+    const size_t nb1 = static_cast<size_t>(k1_grid.x) * k1_grid.y, nb2 = static_cast<size_t>(k2_grid.x) * k2_grid.y;
+    CK(cudaMalloc(&ctl, sizeof(Ctl)));
+    CK(cudaMalloc(&part1, nb1 * sizeof(double)));
+    CK(cudaMalloc(&part2, 2 * std::max(nb2, static_cast<size_t>(norms_grid.x) * norms_grid.y) * sizeof(double)));
+    CK(cudaMalloc(&norms, 4 * sizeof(double)));
+    if (c.trace_len > 0) {
+        CK(cudaMalloc(&trace, static_cast<size_t>(c.trace_len) * 3 * sizeof(double)));
+        CK(cudaMemsetAsync(trace, 0, static_cast<size_t>(c.trace_len) * 3 * sizeof(double), stream));
+    }
+    CK(cudaMallocHost(&h_ctl, 2 * sizeof(Ctl)));
+    CK(cudaEventCreate(&ev_start));
+    CK(cudaEventCreate(&ev_stop));
+    for (auto &e : ev_poll) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    st = run_setup();
+    if (st != PB200_OK) return st;
+    CK(cudaStreamSynchronize(stream));
+    t_setup = now_s() - t0;
+    return PB200_OK;
+}
+
+pb200_status Solver::run_setup() {
+    dim3 grid((f.g.pitch + 255) / 256, f.g.nx + 2);
+    setup_kernel<<<grid, 256, 0, stream>>>(f.g, c, f.a, f.b, f.D, f.r, f.w, f.p[0], f.p[1], f.Ap);
+    ++launches;
+    CK(cudaGetLastError());
+    return PB200_OK;
+}
+
+void Solver::launch_iteration(long long k, bool first) {
+    K1Args a1{};
+    a1.r = f.r;
+    a1.D = f.D;
+    a1.p_old = f.p[(k - 1) & 1];
+    a1.a = f.a;
+    a1.b = f.b;
+    a1.p_new = f.p[k & 1];
+    a1.Ap = f.Ap;
+    a1.partials = part1;
+    a1.ctl = ctl;
+    a1.g = f.g;
+    a1.c = c;
+    a1.rows_per_seg = rows_per_seg;
+    if (first) k1_kernel<true><<<k1_grid, K1_THREADS, 0, stream>>>(a1);
+    else k1_kernel<false><<<k1_grid, K1_THREADS, 0, stream>>>(a1);
+    if (c.multi) allreduce(0, 1);
+    K2Args a2{};
+    a2.w = f.w;
+    a2.r = f.r;
+    a2.p = f.p[k & 1];
+    a2.Ap = f.Ap;
+    a2.D = f.D;
+    a2.partials = part2;
+    a2.trace = trace;
+    a2.ctl = ctl;
+    a2.g = f.g;
+    a2.c = c;
+    k2_kernel<0><<<k2_grid, K2_THREADS, 0, stream>>>(a2);
+    if (c.multi) {
+        exchange_r_halo();
+        allreduce(1, 2);
+        finalize_kernel<<<1, 1, 0, stream>>>(ctl, c, trace, 0);
+    }
+}
+
+int Solver::kernels_per_iteration() const { return c.multi ? 3 + halo_kernels_per_iteration() : 2; }
+
+pb200_status Solver::solve(pb200_result *res) {
+    const double t0 = now_s();
+    CK(cudaSetDevice(dev));
+    if (c.multi && !comm_ready()) { set_error("nranks > 1 but no communicator attached (pb200_attach_comm)"); return PB200_ERR_COMM; }
+    if (solved) { // a second solve on the same handle starts from scratch (S4:803-834)
+        pb200_status st = run_setup();
+        if (st != PB200_OK) return st;
+    }
+    const long long launches0 = launches;
+    // ---- init (S4:803-843): w = 0 and r = B were written by setup; zr_old = (D^-1 r, r)
+    CK(cudaMemsetAsync(ctl, 0, sizeof(Ctl), stream));
+    CK(cudaMemsetAsync(norms, 0, 4 * sizeof(double), stream));
+    {
+        K2Args a2{};
+        a2.w = f.w;
+        a2.r = f.r;
+        a2.p = f.p[0];
+        a2.Ap = f.Ap;
+        a2.D = f.D;
+        a2.partials = part2;
+        a2.ctl = ctl;
+        a2.g = f.g;
+        a2.c = c;
+        k2_kernel<1><<<k2_grid, K2_THREADS, 0, stream>>>(a2);
+        ++launches;
+        if (c.multi) {
+            allreduce(2, 1);
+            finalize_kernel<<<1, 1, 0, stream>>>(ctl, c, trace, 1);
+            ++launches;
+        }
+        CK(cudaGetLastError());
+    }
+
+    // ---- loop (S4:845-943)
+    const double pts_local = static_cast<double>(f.g.nx) * f.g.ny;
+    int check = prm.check_every;
+    if (check <= 0) { // poll roughly every 250 us of device work
+        const double t_it = std::max(6e-6, pts_local * 112.0 / 6.0e12);
+        check = static_cast<int>(std::min(64.0, std::max(2.0, 250e-6 / t_it)));
+    }
+    check += check & 1; // even: graph replays cover two iterations
+    const bool use_graph = prm.use_graph != 0;
+    CK(cudaEventRecord(ev_start, stream));
+    long long k = 1;
+    launch_iteration(k, true); // iteration 1: p = z (S4:830)
+    launches += kernels_per_iteration();
+    ++k;
+    CK(cudaGetLastError());
+    if (use_graph && !graph_exec && c.max_iter > 1) {
+        cudaGraph_t graph = nullptr;
+        CK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+        launch_iteration(2, false);
+        launch_iteration(3, false);
+        CK(cudaStreamEndCapture(stream, &graph));
+        CK(cudaGraphInstantiate(&graph_exec, graph, 0));
+        cudaGraphDestroy(graph);
+    }
+    int slot = 0, pending = -1;
+    bool done = false;
+    long long since_poll = 1;
+    while (!done && k <= c.max_iter) {
+        if (use_graph && graph_exec) {
+            CK(cudaGraphLaunch(graph_exec, stream)); // iterations k, k+1 (the second is a no-op past the end)
+            launches += 2 * kernels_per_iteration();
+            k += 2;
+            since_poll += 2;
+        } else {
+            launch_iteration(k, false);
+            launches += kernels_per_iteration();
+            ++k;
+            ++since_poll;
+        }
+        if (since_poll >= check || k > c.max_iter) {
+            since_poll = 0;
+            CK(cudaMemcpyAsync(&h_ctl[slot], ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, stream));
+            CK(cudaEventRecord(ev_poll[slot], stream));
+            if (pending >= 0) { // look at the batch BEFORE the one just queued: the GPU never idles
+                CK(cudaEventSynchronize(ev_poll[pending]));
+                done = h_ctl[pending].done != 0;
+            }
+            pending = slot;
+            slot ^= 1;
+        }
+    }
+    CK(cudaEventRecord(ev_stop, stream));
+    CK(cudaGetLastError());
+    // ---- results
+    {
+        norms_kernel<<<norms_grid, 256, 0, stream>>>(f.g, f.w, f.r, part2, &ctl->ticket[1], norms);
+        ++launches;
+    }
+    double h_norms[4] = {0, 0, 0, 0};
+    if (c.multi) { // sums and max over all ranks, in stream
+        pb200_status st = reduce_norms_host(h_norms);
+        if (st != PB200_OK) return st;
+    }
+    CK(cudaMemcpyAsync(&h_ctl[0], ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, stream));
+    CK(cudaMemcpyAsync(h_norms, norms, 3 * sizeof(double), cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    CK(cudaGetLastError());
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, ev_start, ev_stop));
+    const Ctl &hc = h_ctl[0];
+    solved = true;
+    last_iter = hc.iter;
+    if (res) {
+        std::memset(res, 0, sizeof(*res));
+        res->iterations = hc.iter;
+        res->stop_reason = hc.status;
+        res->first_converged_iter = hc.conv_iter;
+        res->diff_norm = hc.diff;
+        res->zr = hc.zr_old;
+        res->alpha = hc.alpha;
+        res->beta = hc.beta;
+        res->w_norm_E = std::sqrt(h_norms[0] * c.h1 * c.h2);
+        res->r_norm_E = std::sqrt(h_norms[1] * c.h1 * c.h2);
+        res->w_max = h_norms[2];
+        res->t_setup_s = t_setup;
+        res->t_solve_s = ms * 1e-3;
+        res->t_total_s = now_s() - t0;
+        const double pts = static_cast<double>(prm.M - 1) * (prm.N - 1);
+        res->pt_it_per_s = res->t_solve_s > 0 ? pts * static_cast<double>(hc.iter) / res->t_solve_s : 0.0;
+        res->algo_gbps = res->pt_it_per_s * 104.0 * 1e-9;
+        res->kernel_launches = launches - launches0;
+    }
+    return PB200_OK;
+}
+
+pb200_status Solver::get_solution(double *host, int64_t ld) {
+    if (!solved) { set_error("get_solution before solve"); return PB200_ERR_STATE; }
+    if (!host || ld < prm.N + 1) { set_error("bad host array / ld"); return PB200_ERR_INVALID; }
+    CK(cudaSetDevice(dev));
+    CK(cudaMemcpy2DAsync(host + static_cast<size_t>(i0) * ld + j0, ld * sizeof(double), f.w + f.g.pitch + 1,
+                         f.g.pitch * sizeof(double), f.g.ny * sizeof(double), f.g.nx, cudaMemcpyDeviceToHost, stream));
+    CK(cudaStreamSynchronize(stream));
+    return PB200_OK;
+}
+
+pb200_status Solver::get_trace(double *host, int n, int *rows) {
+    if (!solved) { set_error("get_trace before solve"); return PB200_ERR_STATE; }
+    const int have = static_cast<int>(std::min<long long>(std::min(n, c.trace_len), last_iter));
+    if (rows) *rows = have;
+    if (have > 0) {
+        CK(cudaSetDevice(dev));
+        CK(cudaMemcpy(host, trace, static_cast<size_t>(have) * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+    }
+    return PB200_OK;
+}
+
+} // namespace pb200

@@ -1,0 +1,82 @@
+// pb200_solver.h -- internal C++ interface between the solver, the communicator and the C ABI.
+#pragma once
+#include "../../include/poisson_b200.h"
+#include "pb200_kernels.cuh"
+
+namespace pb200 {
+
+extern thread_local char g_err[512];
+void set_error(const char *fmt, ...);
+
+#define CK(call)                                                                                       \
+    do {                                                                                               \
+        cudaError_t e__ = (call);                                                                      \
+        if (e__ != cudaSuccess) {                                                                      \
+            ::pb200::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+            return PB200_ERR_CUDA;                                                                     \
+        }                                                                                              \
+    } while (0)
+
+void choose_process_grid(int size, int &Px, int &Py);
+void decompose_2d(int M, int N, int Px, int Py, int rank, int &i0, int &i1, int &j0, int &j1);
+pb200_status validate(const pb200_params &p);
+Consts make_consts(const pb200_params &p);
+int pitch_for(int ny);
+
+// The eight device arrays of one block (the reference's d_a..d_Ap, S4:738-749, plus the stored
+// diagonal D and a second p for the ping-pong; no d_B: r is initialised in place, no d_z: z is
+// never stored).
+struct Fields {
+    Geom g{};
+    size_t elems = 0;
+    double *a = nullptr, *b = nullptr, *D = nullptr, *w = nullptr, *r = nullptr, *p[2] = {nullptr, nullptr}, *Ap = nullptr;
+    ~Fields();
+    pb200_status allocate(const Geom &geom);
+    void release();
+};
+
+struct Comm; // pb200_comm.cu
+
+struct Solver {
+    pb200_params prm{};
+    Consts c{};
+    Fields f;
+    int dev = -1;
+    int Px = 1, Py = 1, i0 = 1, i1 = 1, j0 = 1, j1 = 1;
+    cudaStream_t stream = nullptr;
+    Ctl *ctl = nullptr;
+    Ctl *h_ctl = nullptr; // pinned, 2 slots
+    double *part1 = nullptr, *part2 = nullptr, *trace = nullptr, *norms = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr, ev_poll[2] = {nullptr, nullptr};
+    cudaGraphExec_t graph_exec = nullptr;
+    dim3 k1_grid, k2_grid, norms_grid;
+    int rows_per_seg = 32;
+    long long launches = 0;
+    long long last_iter = 0;
+    double t_setup = 0.0;
+    bool solved = false;
+    Comm *comm = nullptr;
+
+    ~Solver();
+    pb200_status create(const pb200_params &params);
+    pb200_status run_setup();
+    void plan_launch();
+    void launch_iteration(long long k, bool first);
+    int kernels_per_iteration() const;
+    pb200_status solve(pb200_result *res);
+    pb200_status get_solution(double *host, int64_t ld);
+    pb200_status get_trace(double *host, int n, int *rows);
+
+    // multi-GPU (pb200_comm.cu)
+    pb200_status attach_comm(const uint8_t id[128]);
+    bool comm_ready() const;
+    void destroy_comm();
+    void allreduce(int first, int count); // in place on ctl->red[first .. first+count)
+    void exchange_r_halo();               // boundary rows/columns of r -> neighbours' ring
+    int halo_kernels_per_iteration() const;
+    pb200_status reduce_norms_host(double h_norms[4]);
+};
+
+pb200_status comm_unique_id(uint8_t id_out[128]);
+
+} // namespace pb200

@@ -1,0 +1,288 @@
+"""Parity of the CUDA path (through the C ABI of libpoisson_b200.so) with the CPU oracle and with
+the golden fixtures generated from the reference. Bars (north_star / SURVEY.md 8(c)):
+  * element-wise operators (setup, A, D^-1, the updates): BIT-EXACT;
+  * inner products: 1e-13 relative (summation order differs);
+  * whole solves: iteration count exact, norms <= 1e-10 relative up to 400x600; above that the
+    reference's own summation-order spread (~1e-9) is the bar.
+"""
+import numpy as np
+import pytest
+
+from __graft_entry__ import load_package
+from oracle_lib import seeded_field
+
+pb = load_package()
+pytestmark = pytest.mark.gpu
+
+RTOL_NORM = 1e-10   # north_star: norms within 1e-10 relative in fp64
+RTOL_DOT = 1e-13    # a reduction in another order
+
+
+def rel(a, b):
+    return abs(a - b) / max(abs(b), 1e-300)
+
+
+def steps(m, n):
+    return 2.0 / m, 1.2 / n
+
+
+# --------------------------------------------------------------------------------------------
+# division by a grid-uniform constant (used four times per point by the stencil)
+
+@pytest.mark.parametrize("h", [2.0 / 40, 1.2 / 40, 2.0 / 400, 1.2 / 600, 2.0 / 2400, 1.2 / 3200, 2.0 / 8192,
+                               1.2 / 8192, 2.0 / 32768, 1.2 / 32768, 2.0 / 37, 1.2 / 53, 1.0 / 3.0, 0.1,
+                               1.9999999999999998, 1.0000000000000002])
+def test_div_const_is_ieee_division(h):
+    assert pb.selftest_div(h, n=1 << 21, seed=20260711) == 0
+
+
+# --------------------------------------------------------------------------------------------
+# coefficient / RHS / diagonal kernel
+
+@pytest.mark.parametrize("m,n,p,rank", [(40, 40, 1, 0), (37, 53, 1, 0), (400, 600, 8, 5), (400, 600, 8, 0),
+                                       (53, 37, 6, 4), (10, 10, 1, 0)])
+def test_setup_bit_exact(oracle, m, n, p, rank):
+    px, py = pb.choose_process_grid(p)
+    blk = pb.decompose_2d(m, n, px, py, rank)
+    a, b, B, D = pb.op_setup(pb.default_params(m, n), blk)
+    oa, ob, oB = oracle.setup(m, n, blk)
+    assert np.array_equal(a, oa) and np.array_equal(b, ob) and np.array_equal(B, oB)
+    h1, h2 = steps(m, n)
+    oD = oracle.diag(oa, ob, h1, h2)
+    assert np.array_equal(D[1:-1, 1:-1], oD[1:-1, 1:-1])
+
+
+def test_setup_against_reference_fixture(golden_arrays):
+    a, b, B, _ = pb.op_setup(pb.default_params(40, 40))
+    assert np.array_equal(a, golden_arrays["a_full40"])
+    assert np.array_equal(b, golden_arrays["b_full40"])
+    assert np.array_equal(B, golden_arrays["B_full40"])
+
+
+def test_setup_other_ellipse_and_eps(oracle):
+    prm = pb.default_params(48, 36, ell_k=1.5, eps=1e-3, f_val=2.5)
+    a, b, B, _ = pb.op_setup(prm)
+    oa, ob, oB = oracle.setup(48, 36, pb=oracle.problem(ell_k=1.5, eps=1e-3, f_val=2.5))
+    assert np.array_equal(a, oa) and np.array_equal(b, ob) and np.array_equal(B, oB)
+
+
+# --------------------------------------------------------------------------------------------
+# operators on seeded inputs; shapes chosen to hit every edge of the kernel's tiling
+# (62-column warp windows, 8-row segments, 2-column vectors, single row / single column)
+
+SHAPES = [(39, 39), (1, 1), (1, 70), (70, 1), (2, 2), (7, 61), (8, 62), (9, 63), (17, 64), (16, 123), (33, 124),
+          (5, 125), (12, 495), (11, 496), (10, 497), (64, 1000), (130, 67)]
+
+
+@pytest.mark.parametrize("nx,ny", SHAPES)
+def test_apply_A_bit_exact(oracle, nx, ny):
+    m, n = nx + 1, ny + 1
+    h1, h2 = steps(m, n)
+    a, b, _ = oracle.setup(m, n) if min(m, n) >= 2 else (None, None, None)
+    p = seeded_field(nx, ny, seed=11)          # halo ring filled too: A must use it (S4:851)
+    got = pb.op_apply_A(pb.default_params(m, n), p, a, b)
+    want = oracle.apply_A(p, a, b, h1, h2)
+    assert np.array_equal(got, want)
+
+
+def test_apply_A_random_coefficients(oracle):
+    nx, ny = 45, 130
+    h1, h2 = steps(nx + 1, ny + 1)
+    a = np.abs(seeded_field(nx, ny, seed=1)) * 1e3 + 0.5
+    b = np.abs(seeded_field(nx, ny, seed=2)) * 1e3 + 0.5
+    p = seeded_field(nx, ny, seed=3) * 1e-7
+    got = pb.op_apply_A(pb.default_params(nx + 1, ny + 1), p, a, b)
+    assert np.array_equal(got, oracle.apply_A(p, a, b, h1, h2))
+
+
+def test_apply_A_against_reference_fixture(golden_arrays):
+    p = seeded_field(39, 39, seed=1234)
+    got = pb.op_apply_A(pb.default_params(40, 40), p, golden_arrays["a_full40"], golden_arrays["b_full40"])
+    assert np.array_equal(got, golden_arrays["Ap_full40"])
+
+
+@pytest.mark.parametrize("nx,ny", [(39, 39), (1, 1), (9, 63), (33, 124), (64, 1000)])
+def test_apply_Dinv_bit_exact(oracle, nx, ny):
+    m, n = nx + 1, ny + 1
+    h1, h2 = steps(m, n)
+    a, b, _ = oracle.setup(m, n)
+    r = seeded_field(nx, ny, seed=4321)
+    got = pb.op_apply_Dinv(pb.default_params(m, n), r, a, b)
+    assert np.array_equal(got, oracle.apply_Dinv(r, a, b, h1, h2))
+
+
+def test_apply_Dinv_against_reference_fixture(golden_arrays):
+    r = seeded_field(39, 39, seed=4321)
+    got = pb.op_apply_Dinv(pb.default_params(40, 40), r, golden_arrays["a_full40"], golden_arrays["b_full40"])
+    assert np.array_equal(got, golden_arrays["z_full40"])
+
+
+@pytest.mark.parametrize("nx,ny", [(39, 39), (1, 1), (300, 513), (1000, 64)])
+def test_dot(oracle, golden, nx, ny):
+    h1, h2 = steps(nx + 1, ny + 1)
+    u, v = seeded_field(nx, ny, seed=1234), seeded_field(nx, ny, seed=4321)
+    got = pb.op_dot(pb.default_params(nx + 1, ny + 1), u, v)
+    assert rel(got, oracle.dot(u, v, h1, h2)) < RTOL_DOT
+    if (nx, ny) == (39, 39):
+        assert rel(got, golden["dot_full40"]) < RTOL_DOT
+
+
+@pytest.mark.parametrize("nx,ny,first", [(39, 39, False), (39, 39, True), (1, 1, False), (9, 63, False),
+                                         (130, 67, False), (64, 1000, False)])
+def test_fused_iteration(oracle, nx, ny, first):
+    """One K1+K2 pass on caller data: every element-wise result bit-exact, scalars to RTOL_DOT."""
+    m, n = nx + 1, ny + 1
+    h1, h2 = steps(m, n)
+    a, b, _ = oracle.setup(m, n)
+    w = seeded_field(nx, ny, seed=5, halo=False)
+    r = seeded_field(nx, ny, seed=6, halo=False)
+    p = seeded_field(nx, ny, seed=7, halo=False)
+    beta, zr_old = 0.37, 0.0123
+    gw, gr, gp, gAp, (denom, alpha, diff2, zr) = pb.op_iteration(pb.default_params(m, n), w, r, p, a, b, beta, zr_old,
+                                                                 first)
+    z = oracle.apply_Dinv(r, a, b, h1, h2)
+    p_new = z.copy() if first else z + beta * p          # numpy: one rounding per operation, like -fmad=false
+    p_new[0, :] = p_new[-1, :] = 0.0
+    p_new[:, 0] = p_new[:, -1] = 0.0
+    assert np.array_equal(gp[1:-1, 1:-1], p_new[1:-1, 1:-1])
+    Ap = oracle.apply_A(p_new, a, b, h1, h2)
+    assert np.array_equal(gAp[1:-1, 1:-1], Ap[1:-1, 1:-1])
+    assert rel(denom, oracle.dot(Ap, p_new, h1, h2)) < RTOL_DOT
+    assert alpha == zr_old / denom
+    w_new = w + alpha * p_new
+    r_new = r - alpha * Ap
+    assert np.array_equal(gw[1:-1, 1:-1], w_new[1:-1, 1:-1])
+    assert np.array_equal(gr[1:-1, 1:-1], r_new[1:-1, 1:-1])
+    d = (w_new - w)[1:-1, 1:-1]
+    assert rel(diff2, float((d * d).sum())) < RTOL_DOT
+    r_full = r.copy()
+    r_full[1:-1, 1:-1] = r_new[1:-1, 1:-1]
+    z_new = oracle.apply_Dinv(r_full, a, b, h1, h2)
+    assert rel(zr, oracle.dot(z_new, r_full, h1, h2)) < RTOL_DOT
+
+
+# --------------------------------------------------------------------------------------------
+# whole solves
+
+@pytest.mark.parametrize("key", ["10x10", "20x20", "40x40", "37x53", "400x600"])
+def test_solve_matches_reference_and_oracle(oracle, golden, golden_arrays, key):
+    m, n = map(int, key.split("x"))
+    tl = 64
+    with pb.Solver(pb.default_params(m, n, trace_len=tl)) as s:
+        res = s.solve()
+        w = s.solution()
+        trace = s.trace(tl)
+    assert res.iterations == golden["iters_stage3"][key]          # unmodified reference solve_mpi
+    assert res.stop_reason == pb.STOP_CONVERGED and res.first_converged_iter == res.iterations
+    ores, ow, otrace = oracle.solve(m, n, want_w=True, trace_len=tl)
+    assert res.iterations == ores.iterations
+    for f, of in (("w_norm_E", "w_norm_E"), ("w_max", "w_max"), ("diff_norm", "diff_norm"), ("zr", "zr"),
+                  ("alpha", "alpha")):
+        assert rel(getattr(res, f), getattr(ores, of)) < RTOL_NORM, f
+    k = min(tl, res.iterations)
+    np.testing.assert_allclose(trace[:k], otrace[:k], rtol=1e-9, atol=0)
+    np.testing.assert_allclose(w, ow, rtol=0, atol=1e-11)
+    assert not w[0].any() and not w[-1].any() and not w[:, 0].any() and not w[:, -1].any()   # Dirichlet ring
+    if key in golden["solves_stage3"]:
+        g = golden["solves_stage3"][key]
+        for f in ("w_norm_E", "w_max", "diff_norm", "zr", "alpha"):
+            assert rel(getattr(res, f), g[f]) < RTOL_NORM, (f, getattr(res, f), g[f])
+        gt = np.array(g["trace"])
+        np.testing.assert_allclose(trace[:len(gt)], gt, rtol=1e-9, atol=0)
+    if key == "40x40":
+        np.testing.assert_allclose(w, golden_arrays["w_40x40"], rtol=0, atol=1e-13)
+
+
+@pytest.mark.parametrize("key", ["10x10", "20x20", "40x40"])
+def test_solve_stage0_norm(oracle, golden, key):
+    """configs[0]: the stage0 serial solver's unweighted stopping norm and signed denominator guard."""
+    m, n = map(int, key.split("x"))
+    res, w = pb.run(pb.default_params(m, n, norm_mode=pb.NORM_STAGE0), want_w=True)
+    assert res.iterations == golden["iters_stage0"][key]
+    ores, ow, _ = oracle.solve(m, n, norm_mode=1, want_w=True)
+    assert rel(res.w_norm_E, ores.w_norm_E) < RTOL_NORM and rel(res.diff_norm, ores.diff_norm) < RTOL_NORM
+    np.testing.assert_allclose(w, ow, rtol=0, atol=1e-12)
+
+
+def test_solve_800x1200(oracle, golden):
+    res, _ = pb.run(pb.default_params(800, 1200))
+    g = golden["solves_stage3"]["800x1200"]
+    assert res.iterations == golden["iters_stage3"]["800x1200"] == 989
+    # at this size the reference's own results move by ~8e-10 with summation order
+    assert rel(res.w_norm_E, g["w_norm_E"]) < 5e-9
+    assert rel(res.diff_norm, g["diff_norm"]) < 1e-9
+    assert rel(res.w_max, g["w_max"]) < 5e-9
+
+
+def test_graph_and_plain_launches_agree_bitwise():
+    outs = []
+    for use_graph, check in ((1, 0), (0, 0), (1, 2), (0, 7)):
+        with pb.Solver(pb.default_params(120, 90, use_graph=use_graph, check_every=check)) as s:
+            res = s.solve()
+            outs.append((res.iterations, res.diff_norm, res.zr, s.solution()))
+    for o in outs[1:]:
+        assert o[0] == outs[0][0] and o[1] == outs[0][1] and o[2] == outs[0][2]
+        assert np.array_equal(o[3], outs[0][3])
+
+
+def test_resolve_on_same_handle_is_deterministic():
+    with pb.Solver(pb.default_params(100, 140)) as s:
+        r1 = s.solve()
+        w1 = s.solution()
+        r2 = s.solve()
+        w2 = s.solution()
+    assert r1.iterations == r2.iterations and r1.zr == r2.zr and np.array_equal(w1, w2)
+
+
+def test_fixed_iters_and_max_iter(oracle):
+    res, _ = pb.run(pb.default_params(40, 40, fixed_iters=57))
+    assert res.iterations == 57 and res.stop_reason == pb.STOP_MAX_ITER and res.first_converged_iter == 50
+    ores, _, _ = oracle.solve(40, 40, fixed_iters=57)
+    assert rel(res.w_norm_E, ores.w_norm_E) < RTOL_NORM
+    res, _ = pb.run(pb.default_params(40, 40, max_iter=13))
+    assert res.iterations == 13 and res.stop_reason == pb.STOP_MAX_ITER and res.first_converged_iter == 0
+    res, _ = pb.run(pb.default_params(40, 40, max_iter=1))
+    assert res.iterations == 1
+    res, _ = pb.run(pb.default_params(40, 40, max_iter=50))
+    assert res.iterations == 50 and res.stop_reason == pb.STOP_CONVERGED
+
+
+def test_other_problem_parameters(oracle):
+    kw = dict(ell_k=1.5, eps=1e-3, f_val=2.5, delta=1e-7)
+    res, w = pb.run(pb.default_params(48, 36, **kw), want_w=True)
+    ores, ow, _ = oracle.solve(48, 36, delta=1e-7, pb=oracle.problem(ell_k=1.5, eps=1e-3, f_val=2.5), want_w=True)
+    assert res.iterations == ores.iterations
+    assert rel(res.w_norm_E, ores.w_norm_E) < RTOL_NORM
+    np.testing.assert_allclose(w, ow, rtol=0, atol=1e-11)
+
+
+def test_analytic_solution_error():
+    """max |w - (1-x^2-4y^2)/10| inside D is 6.2e-4 at 400x600."""
+    m, n = 400, 600
+    _, w = pb.run(pb.default_params(m, n), want_w=True)
+    x = -1.0 + np.arange(m + 1) * (2.0 / m)
+    y = -0.6 + np.arange(n + 1) * (1.2 / n)
+    X, Y = np.meshgrid(x, y, indexing="ij")
+    inside = X * X + 4 * Y * Y < 1
+    err = np.abs(w - (1 - X * X - 4 * Y * Y) / 10)[inside].max()
+    assert err == pytest.approx(6.216e-4, rel=5e-3)
+
+
+# --------------------------------------------------------------------------------------------
+# BASELINE.json's full single-GPU size (8192 x 8192): first iterations against the oracle, and
+# size-independent properties.
+
+def test_full_size_first_iterations(oracle):
+    m = n = 8192
+    k = 3
+    with pb.Solver(pb.default_params(m, n, fixed_iters=k, trace_len=k)) as s:
+        res = s.solve()
+        trace = s.trace(k)
+        res2 = s.solve()            # determinism at full size
+    ores, _, otrace = oracle.solve(m, n, fixed_iters=k, trace_len=k)
+    assert res.iterations == k
+    np.testing.assert_allclose(trace, otrace, rtol=1e-11, atol=0)
+    assert rel(res.w_norm_E, ores.w_norm_E) < RTOL_NORM
+    assert rel(res.r_norm_E, ores.r_norm_E) < RTOL_NORM
+    assert res.w_max == pytest.approx(ores.w_max, rel=1e-12)
+    assert (res2.zr, res2.diff_norm, res2.w_norm_E) == (res.zr, res.diff_norm, res.w_norm_E)
