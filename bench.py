@@ -1,0 +1,327 @@
+#!/usr/bin/env python
+"""bench.py -- the headline measurement of the fused PCG iteration (BASELINE.json `metric`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (config.workload): the 8192 x 8192 fp64 grid of BASELINE.json configs[3] on one GPU -- the
+configuration `north_star`'s bandwidth target is quoted on; with N GPUs every GPU keeps an
+8192 x 8192-cell block of a (Px*8192) x (Py*8192) grid (weak scaling, Px x Py from the reference's
+choose_process_grid). The grid is synthetic by construction: the problem is fully determined by
+(M, N) and the reference's constants; there is no input data.
+
+A step is one pb200_solve of ITERS fixed iterations on a resident solver handle (coefficients already in
+HBM; the call re-initialises w, r, p and runs exactly ITERS iterations, stop test evaluated but not acted
+on). value = grid-point iterations per second of the whole job, from the device time of the K calls
+(CUDA events on the solver stream inside the library, max over ranks). Each iteration streams ~7 GB at
+8192^2, far more than the 126 MB L2, so no L2 flush is needed between timed iterations.
+
+e2e = the same metric through the one-call C ABI entry pb200_run with HOST buffers: device allocation,
+coefficient kernel, the ITERS iterations, the D2H copy of the solution into pinned host memory, and the
+free -- wall clock around the call.
+
+--impl reference times the reference's own CPU implementation of the path (oracle/_ref: the unmodified
+stage3 OpenMP+MPI hybrid solver built from the reference sources, 1 rank x all host threads) on a bounded
+sample of the same workload.
+"""
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+BLOCK = 8192            # cells per GPU per side
+ITERS = 100             # PCG iterations per step
+REF_ITERS = 4           # iterations per reference step (bounded sample)
+ALGO_BYTES = 104.0      # per grid-point iteration, SURVEY.md 8(d): K1 48 B + K2 56 B
+K1_BYTES, K2_BYTES = 48.0, 56.0
+METRIC = "grid_point_iterations_per_second"
+UNIT = "pt*it/s"
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md: 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.lines, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=lambda: [self.lines.append(ln) for ln in self.proc.stdout], daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def workload(n_gpus, pb):
+    px, py = pb.choose_process_grid(n_gpus)
+    return px * BLOCK, py * BLOCK, px, py
+
+
+def run_reference(args, rank, world):
+    """The reference's CPU path (stage3 hybrid, unmodified sources) on a bounded sample."""
+    if rank != 0:
+        return
+    from oracle_lib import Reference, reference_available
+    cores = os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    M = N = BLOCK
+    line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic"}
+    if not reference_available():
+        line["unavailable"] = "oracle/_ref/libref_stage3.so not present (build it where /root/reference is mounted)"
+        print(json.dumps(line))
+        return
+    ref = Reference()
+    pts = (M - 1) * (N - 1)
+    # stdout of the reference ("Converged ...") is not expected for 4 iterations; keep ours clean anyway
+    for _ in range(args.warmup):
+        ref.solve(M, N, max_iter=REF_ITERS)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        it = ref.solve(M, N, max_iter=REF_ITERS)
+        assert it == REF_ITERS
+    dt = time.perf_counter() - t0
+    value = pts * REF_ITERS * args.steps / dt
+    sample = (f"{M}x{N} grid (one GPU's block of the workload), solve_mpi with max_iter={REF_ITERS} per step, "
+              f"coefficient setup included as in the reference's own timings; 1 rank x {cores} OpenMP threads")
+    line.update({"value": value, "ms_per_step": dt / args.steps * 1e3,
+                 "config": {"workload": f"{M}x{N} fp64 grid, reference stage3 hybrid (hybrid.cpp) on host cores",
+                            "iterations_per_step": REF_ITERS},
+                 "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+                 "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                 "gpu_launches": 0})
+    print(json.dumps(line))
+
+
+def cpu_baseline(seconds_budget=20.0):
+    """Rank 0, N=1: the reference's stage3 solver on the host cores, bounded sample of the same grid."""
+    from oracle_lib import Oracle, Reference, reference_available
+    cores = os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    M = N = BLOCK
+    pts = (M - 1) * (N - 1)
+    if reference_available():
+        ref = Reference()
+        t0 = time.perf_counter()
+        it = ref.solve(M, N, max_iter=REF_ITERS)
+        dt = time.perf_counter() - t0
+        kind, what = "reference", "oracle/_ref libref_stage3.so (unmodified hybrid.cpp)"
+    else:
+        t0 = time.perf_counter()
+        res, _, _ = Oracle().solve(M, N, fixed_iters=REF_ITERS)
+        it = res.iterations
+        dt = time.perf_counter() - t0
+        kind, what = "port", "oracle/liboracle.so (C restatement)"
+    return {"value": pts * it / dt, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{M}x{N}, {it} iterations incl. coefficient setup, {what}, 1 rank x {cores} threads, {dt:.1f} s"}
+
+
+def main():
+    global BLOCK
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--iters", type=int, default=ITERS)
+    ap.add_argument("--block", type=int, default=BLOCK, help="cells per GPU per side (default: the named workload)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            sys.exit("bench.py --gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
+        args.gpus = world
+
+    import numpy as np
+    import torch
+    from __graft_entry__ import load_package
+    pb = load_package()
+    if pb.device_count() < 1:
+        sys.exit("bench.py: no CUDA device and the library has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    BLOCK = args.block
+    M, N, px, py = workload(world, pb)
+    pts = (M - 1) * (N - 1)
+    prm = pb.default_params(M, N, fixed_iters=args.iters, device=local_rank, nranks=world, rank=rank, Px=px, Py=py)
+    solver = pb.Solver(prm)
+    if world > 1:
+        uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(pb.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, 0)
+        solver.attach_comm(bytes(uid.cpu().numpy().tobytes()))
+
+    def barrier():
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        solver.solve()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    t_wall0 = time.perf_counter()
+    dev_s, launches, iters_done = 0.0, 0, 0
+    for _ in range(args.steps):
+        res = solver.solve()
+        dev_s += res.t_device_s
+        launches += res.kernel_launches
+        iters_done += res.iterations
+    barrier()
+    wall_s = time.perf_counter() - t_wall0
+    clocks = sampler.stop()
+    assert iters_done == args.iters * args.steps, (iters_done, args.iters, args.steps)
+    t = torch.tensor([dev_s, wall_s], dtype=torch.float64, device="cuda")
+    if dist:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_s, wall_s = t.tolist()
+    value = pts * args.iters * args.steps / dev_s
+
+    # ---- roofline of the dominant kernel (N=1; per-kernel CUDA events inside the library)
+    roofline = None
+    if world == 1:
+        k1_ms, k2_ms = solver.profile_iteration(20)
+        peak, peak_src = measured_peak_gbs()
+        dom, dom_ms, dom_bytes = ("k1_kernel", k1_ms, K1_BYTES) if k1_ms >= k2_ms else ("k2_kernel", k2_ms, K2_BYTES)
+        achieved = pts * dom_bytes / (dom_ms * 1e-3) * 1e-9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")     # dram bytes per launch from the last ncu --set full capture
+        if os.path.exists(tp):
+            try:
+                traffic = json.load(open(tp)).get(f"{dom}@{M}x{N}")
+            except Exception:
+                traffic = None
+        roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": pts * dom_bytes,
+                    "k1_ms": k1_ms, "k2_ms": k2_ms,
+                    "k1_gbs": pts * K1_BYTES / (k1_ms * 1e-3) * 1e-9, "k2_gbs": pts * K2_BYTES / (k2_ms * 1e-3) * 1e-9,
+                    "iteration_gbs": pts * ALGO_BYTES / ((k1_ms + k2_ms) * 1e-3) * 1e-9,
+                    "iteration_frac": pts * ALGO_BYTES / ((k1_ms + k2_ms) * 1e-3) * 1e-9 / peak}
+    solver.close()
+
+    # ---- e2e: one-call C ABI with host buffers (alloc + setup + iterations + D2H into pinned memory + free)
+    e2e = None
+    if world == 1:
+        w_host = torch.empty((M + 1, N + 1), dtype=torch.float64).pin_memory()
+        lib = pb.lib()
+        prm1 = pb.default_params(M, N, fixed_iters=args.iters, device=local_rank)
+        res = pb.Result()
+        wp = ctypes.cast(w_host.data_ptr(), ctypes.POINTER(ctypes.c_double))
+        times = []
+        for i in range(3):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            st = lib.pb200_run(ctypes.byref(prm1), ctypes.byref(res), wp, N + 1)
+            torch.cuda.synchronize()
+            times.append(time.perf_counter() - t0)
+            assert st == 0 and res.iterations == args.iters
+        t_e2e = min(times[1:])
+        assert float(w_host.abs().max()) > 0
+        e2e = {"value": pts * args.iters / t_e2e, "unit": UNIT, "h2d_bytes_per_step": ctypes.sizeof(prm1),
+               "d2h_bytes_per_step": (M - 1) * (N - 1) * 8, "ms_per_call": t_e2e * 1e3,
+               "call": "pb200_run(params, result, w_host, ld): cudaMalloc + coefficient kernel + iterations + solution D2H + cudaFree"}
+        del w_host
+    else:
+        # multi-GPU: create + attach + solve + solution D2H per rank, wall clock, max over ranks
+        barrier()
+        t0 = time.perf_counter()
+        s2 = pb.Solver(prm)
+        s2.attach_comm(bytes(uid.cpu().numpy().tobytes()))
+        r2 = s2.solve()
+        i0, i1, j0, j1 = pb.decompose_2d(M, N, px, py, rank)
+        blk = torch.empty((i1 - i0 + 1, N + 1), dtype=torch.float64).pin_memory()
+        # block rows land in a pinned staging array addressed as the whole grid (row offset folded into the pointer)
+        base = blk.data_ptr() - i0 * (N + 1) * 8
+        st = pb.lib().pb200_get_solution(s2.h, ctypes.cast(base, ctypes.POINTER(ctypes.c_double)), N + 1)
+        assert st == 0 and r2.iterations == args.iters
+        barrier()
+        t2 = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        s2.close()
+        e2e = {"value": pts * args.iters / t2.item(), "unit": UNIT, "h2d_bytes_per_step": 128 + ctypes.sizeof(prm),
+               "d2h_bytes_per_step": (M - 1) * (N - 1) * 8, "ms_per_call": t2.item() * 1e3,
+               "call": "pb200_create + pb200_attach_comm + pb200_solve + pb200_get_solution per rank"}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": f"{M}x{N} fp64 grid ({px}x{py} blocks of {BLOCK}x{BLOCK} cells, one per GPU), "
+                                       f"fused PCG iteration, fixed {args.iters} iterations per step",
+                           "grid": [M, N], "process_grid": [px, py], "iterations_per_step": args.iters,
+                           "l2": "inputs larger than L2 (each iteration streams ~7 GB per GPU)",
+                           "timing": "CUDA events on the solver stream inside pb200_solve, summed over steps, max over ranks"},
+                "algo_gbs": value * ALGO_BYTES * 1e-9, "algo_gbs_per_gpu": value * ALGO_BYTES * 1e-9 / world,
+                "wall_ms_per_step": wall_s / args.steps * 1e3,
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches)}
+        if roofline:
+            line["roofline"] = roofline
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline()
+        print(json.dumps(line))
+    if dist:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -88,7 +88,8 @@ typedef struct pb200_result {
     double pt_it_per_s;          /* (M-1)(N-1) * iterations / t_solve_s, whole job */
     double algo_gbps;            /* pt_it_per_s * 104 B */
     int64_t kernel_launches;     /* launches of this library's kernels during the call */
-    double reserved[6];
+    double t_device_s;           /* device time of the whole pb200_solve call (re-setup, init, loop, norms), CUDA events */
+    double reserved[5];
 } pb200_result;
 
 typedef struct pb200_solver pb200_solver;
@@ -126,6 +127,10 @@ pb200_status pb200_get_trace(pb200_solver *s, double *host_3n, int32_t n, int32_
 /* Device pointer + pitch (in doubles) of a field of this block, for callers that stay on the GPU.
  * which: 0 w, 1 r, 2 p, 3 Ap, 4 a, 5 b, 6 D. Rows li=0..nx+1, columns lj=0..ny+1 at ptr[li*pitch+lj]. */
 pb200_status pb200_get_field(pb200_solver *s, int32_t which, double **dev_ptr, int64_t *pitch, int32_t *nx, int32_t *ny);
+/* Measurement aid (bench.py's roofline): restarts from the initial state, runs `iters` iterations as plain
+ * launches with CUDA events on the solver stream around each kernel, and returns the mean duration in
+ * milliseconds of K1 (ms_out[0]: p-update + A p + (Ap,p)) and K2 (ms_out[1]: w,r update + norms). Single rank. */
+pb200_status pb200_profile_iteration(pb200_solver *s, int32_t iters, double ms_out[2]);
 void pb200_destroy(pb200_solver *s);
 
 /* One call = the reference binary's whole solver phase: create + solve (+ solution to host when

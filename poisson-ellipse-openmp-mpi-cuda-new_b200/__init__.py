@@ -42,7 +42,7 @@ class Result(C.Structure):
                 ("w_norm_E", C.c_double), ("r_norm_E", C.c_double), ("w_max", C.c_double),
                 ("t_setup_s", C.c_double), ("t_solve_s", C.c_double), ("t_total_s", C.c_double),
                 ("pt_it_per_s", C.c_double), ("algo_gbps", C.c_double), ("kernel_launches", C.c_int64),
-                ("reserved", C.c_double * 6)]
+                ("t_device_s", C.c_double), ("reserved", C.c_double * 5)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
@@ -56,7 +56,7 @@ class PB200Error(RuntimeError):
 EXPORTS = ["pb200_api_version", "pb200_status_string", "pb200_last_error", "pb200_device_count",
            "pb200_default_params", "pb200_choose_process_grid", "pb200_decompose_2d", "pb200_create",
            "pb200_comm_unique_id", "pb200_attach_comm", "pb200_solve", "pb200_get_solution", "pb200_get_trace",
-           "pb200_get_field", "pb200_destroy", "pb200_run", "pb200_op_setup", "pb200_op_apply_A",
+           "pb200_get_field", "pb200_profile_iteration", "pb200_destroy", "pb200_run", "pb200_op_setup", "pb200_op_apply_A",
            "pb200_op_apply_Dinv", "pb200_op_iteration", "pb200_op_dot", "pb200_selftest_div"]
 
 _lib = None
@@ -84,6 +84,7 @@ def lib():
         L.pb200_get_trace.argtypes = [C.c_void_p, c_double_p, C.c_int32, C.POINTER(C.c_int32)]
         L.pb200_get_field.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_int64),
                                       C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+        L.pb200_profile_iteration.argtypes = [C.c_void_p, C.c_int32, c_double_p]
         L.pb200_destroy.argtypes = [C.c_void_p]
         L.pb200_destroy.restype = None
         L.pb200_run.argtypes = [C.POINTER(Params), C.POINTER(Result), c_double_p, C.c_int64]
@@ -180,6 +181,12 @@ class Solver:
         ptr, pitch, nx, ny = C.c_void_p(), C.c_int64(), C.c_int32(), C.c_int32()
         _check(lib().pb200_get_field(self.h, which, C.byref(ptr), C.byref(pitch), C.byref(nx), C.byref(ny)))
         return ptr.value, pitch.value, nx.value, ny.value
+
+    def profile_iteration(self, iters):
+        """Mean milliseconds of K1 and K2 (CUDA events around each launch)."""
+        out = np.zeros(2)
+        _check(lib().pb200_profile_iteration(self.h, iters, _ptr(out)))
+        return float(out[0]), float(out[1])
 
     def close(self):
         if self.h:

@@ -274,6 +274,11 @@ pb200_status pb200_get_field(pb200_solver *s, int32_t which, double **dev_ptr, i
     return PB200_OK;
 }
 
+pb200_status pb200_profile_iteration(pb200_solver *s, int32_t iters, double ms_out[2]) {
+    if (!s || !ms_out) { set_error("null argument"); return PB200_ERR_INVALID; }
+    return s->impl.profile_iteration(iters, ms_out);
+}
+
 void pb200_destroy(pb200_solver *s) { delete s; }
 
 pb200_status pb200_run(const pb200_params *p, pb200_result *res, double *w_host, int64_t ld) {

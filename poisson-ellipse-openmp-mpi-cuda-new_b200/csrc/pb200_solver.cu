@@ -17,6 +17,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <vector>
 
 namespace pb200 {
 
@@ -123,6 +124,8 @@ Solver::~Solver() {
     for (auto &e : ev_poll) if (e) cudaEventDestroy(e);
     if (ev_start) cudaEventDestroy(ev_start);
     if (ev_stop) cudaEventDestroy(ev_stop);
+    if (ev_call0) cudaEventDestroy(ev_call0);
+    if (ev_call1) cudaEventDestroy(ev_call1);
     if (ctl) cudaFree(ctl);
     if (part1) cudaFree(part1);
     if (part2) cudaFree(part2);
@@ -197,6 +200,8 @@ pb200_status Solver::create(const pb200_params &params) {
     CK(cudaMallocHost(&h_ctl, 2 * sizeof(Ctl)));
     CK(cudaEventCreate(&ev_start));
     CK(cudaEventCreate(&ev_stop));
+    CK(cudaEventCreate(&ev_call0));
+    CK(cudaEventCreate(&ev_call1));
     for (auto &e : ev_poll) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     st = run_setup();
     if (st != PB200_OK) return st;
@@ -255,11 +260,12 @@ pb200_status Solver::solve(pb200_result *res) {
     const double t0 = now_s();
     CK(cudaSetDevice(dev));
     if (c.multi && !comm_ready()) { set_error("nranks > 1 but no communicator attached (pb200_attach_comm)"); return PB200_ERR_COMM; }
+    const long long launches0 = launches;
+    CK(cudaEventRecord(ev_call0, stream));
     if (solved) { // a second solve on the same handle starts from scratch (S4:803-834)
         pb200_status st = run_setup();
         if (st != PB200_OK) return st;
     }
-    const long long launches0 = launches;
     // ---- init (S4:803-843): w = 0 and r = B were written by setup; zr_old = (D^-1 r, r)
     CK(cudaMemsetAsync(ctl, 0, sizeof(Ctl), stream));
     CK(cudaMemsetAsync(norms, 0, 4 * sizeof(double), stream));
@@ -349,10 +355,12 @@ pb200_status Solver::solve(pb200_result *res) {
     }
     CK(cudaMemcpyAsync(&h_ctl[0], ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, stream));
     CK(cudaMemcpyAsync(h_norms, norms, 3 * sizeof(double), cudaMemcpyDeviceToHost, stream));
+    CK(cudaEventRecord(ev_call1, stream));
     CK(cudaStreamSynchronize(stream));
     CK(cudaGetLastError());
-    float ms = 0.f;
+    float ms = 0.f, ms_call = 0.f;
     CK(cudaEventElapsedTime(&ms, ev_start, ev_stop));
+    CK(cudaEventElapsedTime(&ms_call, ev_call0, ev_call1));
     const Ctl &hc = h_ctl[0];
     solved = true;
     last_iter = hc.iter;
@@ -375,7 +383,60 @@ pb200_status Solver::solve(pb200_result *res) {
         res->pt_it_per_s = res->t_solve_s > 0 ? pts * static_cast<double>(hc.iter) / res->t_solve_s : 0.0;
         res->algo_gbps = res->pt_it_per_s * 104.0 * 1e-9;
         res->kernel_launches = launches - launches0;
+        res->t_device_s = ms_call * 1e-3;
     }
+    return PB200_OK;
+}
+
+// Measurement aid: mean duration of K1 and of K2 over `iters` iterations from a fresh start,
+// CUDA events on the solver stream around every launch (plain launches, no graph).
+pb200_status Solver::profile_iteration(int iters, double ms_out[2]) {
+    if (c.multi) { set_error("profile_iteration is single-rank"); return PB200_ERR_INVALID; }
+    if (iters < 1) { set_error("iters must be >= 1"); return PB200_ERR_INVALID; }
+    CK(cudaSetDevice(dev));
+    pb200_status st = run_setup();
+    if (st != PB200_OK) return st;
+    CK(cudaMemsetAsync(ctl, 0, sizeof(Ctl), stream));
+    K2Args a2{};
+    a2.w = f.w; a2.r = f.r; a2.p = f.p[0]; a2.Ap = f.Ap; a2.D = f.D; a2.partials = part2; a2.ctl = ctl; a2.g = f.g; a2.c = c;
+    a2.c.fixed = 1;
+    a2.c.max_iter = 1LL << 60;
+    k2_kernel<1><<<k2_grid, K2_THREADS, 0, stream>>>(a2);
+    std::vector<cudaEvent_t> ev(3 * (size_t)iters);
+    for (auto &e : ev) CK(cudaEventCreate(&e));
+    const Consts saved = c;
+    c.fixed = 1;
+    c.max_iter = 1LL << 60;
+    for (int k = 1; k <= iters; ++k) {
+        K1Args a1{};
+        a1.r = f.r; a1.D = f.D; a1.p_old = f.p[(k - 1) & 1]; a1.a = f.a; a1.b = f.b; a1.p_new = f.p[k & 1]; a1.Ap = f.Ap;
+        a1.partials = part1; a1.ctl = ctl; a1.g = f.g; a1.c = c; a1.rows_per_seg = rows_per_seg;
+        a2.p = f.p[k & 1];
+        a2.c = c;
+        cudaEventRecord(ev[3 * (k - 1) + 0], stream);
+        if (k == 1) k1_kernel<true><<<k1_grid, K1_THREADS, 0, stream>>>(a1);
+        else k1_kernel<false><<<k1_grid, K1_THREADS, 0, stream>>>(a1);
+        cudaEventRecord(ev[3 * (k - 1) + 1], stream);
+        k2_kernel<0><<<k2_grid, K2_THREADS, 0, stream>>>(a2);
+        cudaEventRecord(ev[3 * (k - 1) + 2], stream);
+    }
+    c = saved;
+    launches += 2 * iters + 2;
+    CK(cudaStreamSynchronize(stream));
+    CK(cudaGetLastError());
+    double t1 = 0.0, t2 = 0.0;
+    for (int k = 0; k < iters; ++k) {
+        float a = 0.f, b = 0.f;
+        cudaEventElapsedTime(&a, ev[3 * k], ev[3 * k + 1]);
+        cudaEventElapsedTime(&b, ev[3 * k + 1], ev[3 * k + 2]);
+        t1 += a;
+        t2 += b;
+    }
+    for (auto &e : ev) cudaEventDestroy(e);
+    ms_out[0] = t1 / iters;
+    ms_out[1] = t2 / iters;
+    solved = true; // the fields now hold `iters` iterations of a fixed-count run
+    last_iter = iters;
     return PB200_OK;
 }
 

@@ -47,7 +47,7 @@ struct Solver {
     Ctl *ctl = nullptr;
     Ctl *h_ctl = nullptr; // pinned, 2 slots
     double *part1 = nullptr, *part2 = nullptr, *trace = nullptr, *norms = nullptr;
-    cudaEvent_t ev_start = nullptr, ev_stop = nullptr, ev_poll[2] = {nullptr, nullptr};
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr, ev_call0 = nullptr, ev_call1 = nullptr, ev_poll[2] = {nullptr, nullptr};
     cudaGraphExec_t graph_exec = nullptr;
     dim3 k1_grid, k2_grid, norms_grid;
     int rows_per_seg = 32;
@@ -64,6 +64,7 @@ struct Solver {
     void launch_iteration(long long k, bool first);
     int kernels_per_iteration() const;
     pb200_status solve(pb200_result *res);
+    pb200_status profile_iteration(int iters, double ms_out[2]);
     pb200_status get_solution(double *host, int64_t ld);
     pb200_status get_trace(double *host, int n, int *rows);
 
