@@ -159,6 +159,21 @@ pb200_status pb200_op_iteration(const pb200_params *p, double *w, double *r, dou
                                 double out[4]);
 /* h1*h2-weighted inner product over the interior (replaces dot_kernel + dot_gpu, S4:574-598, 772-787). */
 pb200_status pb200_op_dot(const pb200_params *p, const double *u, const double *v, int32_t nx, int32_t ny, double *out);
+/* No counterpart in the reference. The same weighted inner product for callers that cannot allocate device
+ * memory: programs whose GPU memory is wholly owned by their own pool or framework allocator (a cudaMalloc from
+ * this library would fail or fragment it) and latency-critical loops that cannot afford cudaMalloc/cudaFree,
+ * which synchronise the device. Inputs and output are DEVICE pointers supplied by the caller: u, v are blocks in
+ * the solver's layout (rows li = 0..nx+1 of `pitch` doubles, columns lj = 0..ny+1, pitch >= ny+2), *dev_out
+ * receives sum_{interior} u*v * h1 * h2; the launch goes to `cuda_stream` (a cudaStream_t, NULL = default stream)
+ * and the call returns without waiting for it. Nothing is allocated or freed: the block partials live in a
+ * 64 KiB + 256 B array that is part of the library image on every GPU that loads it (held until the process exits).
+ * Limit: ceil(ny/256) * min(nx,512) <= 8192 reduction blocks (e.g. ny <= 4096 when nx >= 512); beyond that the
+ * call fails with PB200_ERR_TOO_LARGE. The array is shared by all calls on a GPU and keeps the last call's
+ * contents (the call re-zeroes what must start at zero): calls that follow one another in a stream are fine,
+ * calls whose kernels overlap on the GPU race. The first call on each device resolves the array's device
+ * address (with that device current); make that first call before any stream capture. */
+pb200_status pb200_dot_noalloc(const double *dev_u, const double *dev_v, int32_t nx, int32_t ny, int64_t pitch,
+                               double h1, double h2, double *dev_out, void *cuda_stream);
 /* Device self-test of the correctly-rounded division by a grid-uniform constant used inside the
  * stencil: compares it with IEEE x/h on n pseudo-random and n adversarial x; *mismatches must be 0. */
 pb200_status pb200_selftest_div(double h, int64_t n, uint64_t seed, int64_t *mismatches);

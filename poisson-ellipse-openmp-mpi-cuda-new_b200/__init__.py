@@ -57,7 +57,7 @@ EXPORTS = ["pb200_api_version", "pb200_status_string", "pb200_last_error", "pb20
            "pb200_default_params", "pb200_choose_process_grid", "pb200_decompose_2d", "pb200_create",
            "pb200_comm_unique_id", "pb200_attach_comm", "pb200_solve", "pb200_get_solution", "pb200_get_trace",
            "pb200_get_field", "pb200_profile_iteration", "pb200_destroy", "pb200_run", "pb200_op_setup", "pb200_op_apply_A",
-           "pb200_op_apply_Dinv", "pb200_op_iteration", "pb200_op_dot", "pb200_selftest_div"]
+           "pb200_op_apply_Dinv", "pb200_op_iteration", "pb200_op_dot", "pb200_dot_noalloc", "pb200_selftest_div"]
 
 _lib = None
 
@@ -94,6 +94,8 @@ def lib():
         L.pb200_op_iteration.argtypes = ([C.POINTER(Params)] + [c_double_p] * 6 + [C.c_int32] * 2 +
                                          [C.c_double, C.c_double, C.c_int32, c_double_p])
         L.pb200_op_dot.argtypes = [C.POINTER(Params)] + [c_double_p] * 2 + [C.c_int32] * 2 + [c_double_p]
+        L.pb200_dot_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int64, C.c_double, C.c_double,
+                                        C.c_void_p, C.c_void_p]
         L.pb200_selftest_div.argtypes = [C.c_double, C.c_int64, C.c_uint64, C.POINTER(C.c_int64)]
         _lib = L
     return _lib
@@ -253,6 +255,13 @@ def op_dot(params, u, v):
     _check(lib().pb200_op_dot(C.byref(params), _ptr(u), _ptr(v), u.shape[0] - 2, u.shape[1] - 2,
                               C.cast(C.byref(out), c_double_p)))
     return out.value
+
+
+def dot_noalloc(dev_u, dev_v, nx, ny, pitch, h1, h2, dev_out, stream=None):
+    """pb200_dot_noalloc: DEVICE pointers (ints) in and out, nothing allocated, asynchronous on `stream`.
+    For callers that cannot call cudaMalloc (memory owned by their own pool, or no-sync loops); capped size,
+    shared built-in scratch -- see include/poisson_b200.h."""
+    _check(lib().pb200_dot_noalloc(dev_u, dev_v, nx, ny, pitch, h1, h2, dev_out, stream))
 
 
 def selftest_div(h, n=1 << 20, seed=1234):

@@ -3,3 +3,4 @@
 #include "pb200_solver.cu"
 #include "pb200_comm.cu"
 #include "pb200_capi.cu"
+#include "pb200_noalloc.cu"
