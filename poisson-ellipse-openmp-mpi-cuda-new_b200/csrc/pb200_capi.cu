@@ -24,8 +24,9 @@ struct OpBlock {
     double *part = nullptr;
     double *out = nullptr;
     cudaStream_t stream = nullptr;
-    dim3 k1_grid, k2_grid;
+    dim3 k1_grid, k2_grid, init_grid;
     int rows_per_seg = 8;
+    bool safe_div = false;
 
     ~OpBlock() {
         if (ctl) cudaFree(ctl);
@@ -59,11 +60,13 @@ struct OpBlock {
         c.trace_len = 0;
         st = f.allocate(g);
         if (st != PB200_OK) return st;
-        for (double *q : {f.a, f.b, f.D, f.w, f.r, f.p[0], f.p[1], f.Ap}) CK(cudaMemset(q, 0, f.elems * sizeof(double)));
+        for (double *q : {f.a, f.b, f.D, f.w, f.r, f.z, f.p[0], f.p[1], f.Ap}) CK(cudaMemset(q, 0, f.elems * sizeof(double)));
         const int wcols = (ny + K1_OWN - 1) / K1_OWN;
         k1_grid = dim3((wcols + K1_WARPS - 1) / K1_WARPS, (nx + rows_per_seg - 1) / rows_per_seg, 1);
         k2_grid = dim3((ny / 2 + 1 + K2_THREADS - 1) / K2_THREADS, (nx + K2_ROWS - 1) / K2_ROWS, 1);
+        init_grid = dim3((g.pitch + INIT_THREADS - 1) / INIT_THREADS, std::min(nx + 2, 1024), 1);
         size_t nb = (size_t)k1_grid.x * k1_grid.y;
+        nb = std::max(nb, (size_t)init_grid.x * init_grid.y);
         nb = std::max(nb, (size_t)k2_grid.x * k2_grid.y);
         nb = std::max(nb, (size_t)((ny + 255) / 256) * (size_t)std::min(nx, 512));
         CK(cudaMalloc(&ctl, sizeof(Ctl)));
@@ -72,6 +75,12 @@ struct OpBlock {
         CK(cudaMalloc(&out, 4 * sizeof(double)));
         CK(cudaMemset(out, 0, 4 * sizeof(double)));
         return PB200_OK;
+    }
+    // caller-supplied coefficients: outside div_const's verified range -> IEEE divides everywhere
+    void scan_coefficients(const double *host) {
+        const size_t n = (size_t)(f.g.nx + 2) * (f.g.ny + 2);
+        for (size_t i = 0; i < n && !safe_div; ++i)
+            if (!coef_in_div_range(host[i])) safe_div = true;
     }
     // host (nx+2)x(ny+2) -> device pitched
     pb200_status put(double *dev, const double *host) {
@@ -106,10 +115,22 @@ struct OpBlock {
         CK(cudaGetLastError());
         return PB200_OK;
     }
-    pb200_status k1(bool first, const double *p_old, double *p_new) {
-        K1Args a{};
+    pb200_status init_z() { // z = D^-1 r on every stored cell, ctl->zr_old = (z, r)
+        InitArgs a{};
         a.r = f.r;
         a.D = f.D;
+        a.z = f.z;
+        a.partials = part;
+        a.ctl = ctl;
+        a.g = f.g;
+        a.c = c;
+        init_kernel<<<init_grid, INIT_THREADS>>>(a);
+        CK(cudaGetLastError());
+        return PB200_OK;
+    }
+    pb200_status k1(bool first, const double *p_old, double *p_new) {
+        K1Args a{};
+        a.z = f.z;
         a.p_old = p_old;
         a.a = f.a;
         a.b = f.b;
@@ -120,8 +141,13 @@ struct OpBlock {
         a.g = f.g;
         a.c = c;
         a.rows_per_seg = rows_per_seg;
-        if (first) k1_kernel<true><<<k1_grid, K1_THREADS>>>(a);
-        else k1_kernel<false><<<k1_grid, K1_THREADS>>>(a);
+        if (first) {
+            if (safe_div) k1_kernel<true, true><<<k1_grid, K1_THREADS>>>(a);
+            else k1_kernel<true, false><<<k1_grid, K1_THREADS>>>(a);
+        } else {
+            if (safe_div) k1_kernel<false, true><<<k1_grid, K1_THREADS>>>(a);
+            else k1_kernel<false, false><<<k1_grid, K1_THREADS>>>(a);
+        }
         CK(cudaGetLastError());
         return PB200_OK;
     }
@@ -129,6 +155,7 @@ struct OpBlock {
         K2Args a{};
         a.w = f.w;
         a.r = f.r;
+        a.z = f.z;
         a.p = p;
         a.Ap = f.Ap;
         a.D = f.D;
@@ -136,7 +163,7 @@ struct OpBlock {
         a.ctl = ctl;
         a.g = f.g;
         a.c = c;
-        k2_kernel<0><<<k2_grid, K2_THREADS>>>(a);
+        k2_kernel<<<k2_grid, K2_THREADS>>>(a);
         CK(cudaGetLastError());
         return PB200_OK;
     }
@@ -319,8 +346,9 @@ pb200_status pb200_op_apply_A(const pb200_params *p, const double *pvec, const d
     TRY(ob.put(ob.f.p[0], pvec));
     TRY(ob.put(ob.f.a, a));
     TRY(ob.put(ob.f.b, b));
-    // r = 0, D = 1, beta = 1: K1 forms p' = 0/1 + 1*p = p exactly, then Ap = A p'
-    TRY(ob.diag());
+    ob.scan_coefficients(a);
+    ob.scan_coefficients(b);
+    // z = 0, beta = 1: K1 forms p' = 0 + 1*p = p exactly, then Ap = A p'
     TRY(ob.set_ctl(1.0, 0.0));
     TRY(ob.k1(false, ob.f.p[0], ob.f.p[1]));
     CK(cudaDeviceSynchronize());
@@ -337,10 +365,9 @@ pb200_status pb200_op_apply_Dinv(const pb200_params *p, const double *r, const d
     TRY(ob.put(ob.f.a, a));
     TRY(ob.put(ob.f.b, b));
     TRY(ob.diag());
-    TRY(ob.set_ctl(0.0, 0.0));
-    TRY(ob.k1(true, ob.f.p[0], ob.f.p[1])); // first-iteration form: p' = D^-1 r
+    TRY(ob.init_z()); // the solver's start-up kernel: z = D^-1 r
     CK(cudaDeviceSynchronize());
-    TRY(ob.get_interior(z, ob.f.p[1]));
+    TRY(ob.get_interior(z, ob.f.z));
     return PB200_OK;
 }
 
@@ -355,7 +382,11 @@ pb200_status pb200_op_iteration(const pb200_params *p, double *w, double *r, dou
     TRY(ob.put(ob.f.p[0], pvec));
     TRY(ob.put(ob.f.a, a));
     TRY(ob.put(ob.f.b, b));
+    ob.scan_coefficients(a);
+    ob.scan_coefficients(b);
     TRY(ob.diag());
+    TRY(ob.init_z());
+    CK(cudaDeviceSynchronize());
     TRY(ob.set_ctl(beta, zr_old));
     TRY(ob.k1(first != 0, ob.f.p[0], ob.f.p[1]));
     TRY(ob.k2(ob.f.p[1]));

@@ -2,9 +2,10 @@
 //
 // Replaces the seven kernels of the reference (stage4-mpi+cuda/poisson_mpi_cuda_f.cu, "S4"):
 //   setup_kernel  <- fictitious_regions_setup_local (host loop, S4:146-192) + zero_kernel (S4:599-609)
-//   k1_kernel     <- apply_Dinv_kernel (S4:541-562) + update_p_kernel (S4:663-676) / copy_kernel (S4:612-623)
-//                    + apply_A_kernel (S4:507-536) + dot_kernel for (Ap,p) (S4:574-598)
-//   k2_kernel     <- update_w_r_kernel (S4:626-660) + apply_Dinv_kernel + dot_kernel for (z,r)
+//   init_kernel   <- apply_Dinv_kernel + dot_kernel at start-up (S4:820-843)
+//   k1_kernel     <- update_p_kernel (S4:663-676) / copy_kernel (S4:612-623) + apply_A_kernel (S4:507-536)
+//                    + dot_kernel for (Ap,p) (S4:574-598)
+//   k2_kernel     <- update_w_r_kernel (S4:626-660) + apply_Dinv_kernel (S4:541-562) + dot_kernel for (z,r)
 //                    + the host-side scalar logic of the loop (S4:872-906, 926-932)
 //
 // Arithmetic contract: every element-wise expression keeps the reference's expression tree with
@@ -233,21 +234,89 @@ __global__ void __launch_bounds__(256) diag_kernel(Geom g, Consts c, const doubl
 }
 
 // ------------------------------------------------------------------------------------------
-// K1: p' = D^-1 r + beta p ; Ap = A p' ; partial (Ap,p').
+// Division helpers for the iteration kernels.
+
+// True when v is zero or 2^-400 <= |v| <= 2^400: products of such values with coefficients in the same
+// range stay inside the interval where div_const's residuals are exact. Integer pipe only.
+__device__ __forceinline__ bool in_div_range(double v) {
+    const unsigned hi = (unsigned)__double2hiint(v) & 0x7fffffffu;
+    const unsigned e = hi >> 20;
+    return (e - 623u <= 800u) || ((hi | (unsigned)__double2loint(v)) == 0u);
+}
+
+// div_const without the per-call range test (the caller has established the range).
+__device__ __forceinline__ double div_const_nocheck(double x, double h, double rh) {
+    double q = __dmul_rn(x, rh);
+    double e = __fma_rn(-h, q, x);
+    q = __fma_rn(e, rh, q);
+    e = __fma_rn(-h, q, x);
+    return __fma_rn(e, rh, q);
+}
+
+// r / D as the reference writes it (S4:559), without the generic divide's slow path for r == 0: the
+// divide sees 1.0 instead of a zero numerator and the zero (with its sign; D > 0 in practice, and the
+// sign of a zero never reaches a non-zero result) is put back afterwards.
+__device__ __forceinline__ double precond_div(double r, double D) {
+    const bool zero = (r == 0.0);
+    const double q = __ddiv_rn(zero ? 1.0 : r, D);
+    return (D != 0.0) ? (zero ? ((D < 0.0) ? -r : r) : q) : 0.0;
+}
+
+// ------------------------------------------------------------------------------------------
+// init: z = D^-1 r on every stored cell (ring included: the ring's r and D were computed by
+// setup_kernel, so no exchange is needed), zr_old = (z, r) over the interior (S4:820-843).
+constexpr int INIT_THREADS = 256;
+
+struct InitArgs {
+    const double *r, *D;
+    double *z;
+    double *partials;
+    Ctl *ctl;
+    Geom g;
+    Consts c;
+};
+
+__global__ void __launch_bounds__(INIT_THREADS) init_kernel(const InitArgs A) {
+    const Geom g = A.g;
+    const int lj = blockIdx.x * blockDim.x + threadIdx.x;
+    double acc[1] = {0.0};
+    if (lj < g.pitch)
+        for (int li = blockIdx.y; li <= g.nx + 1; li += gridDim.y) {
+            const size_t o = (size_t)li * g.pitch + lj;
+            const double r = A.r[o];
+            const double z = (lj <= g.ny + 1) ? precond_div(r, A.D[o]) : 0.0;
+            A.z[o] = z;
+            if (li >= 1 && li <= g.nx && lj >= 1 && lj <= g.ny) acc[0] += z * r; // S4:594
+        }
+    double tot[1];
+    if (grid_reduce<1, INIT_THREADS>(acc, A.partials, &A.ctl->ticket[1], tot)) {
+        const double zr = tot[0] * A.c.h1 * A.c.h2; // S3:191
+        A.ctl->red[2] = zr;
+        if (!A.c.multi) A.ctl->zr_old = zr; // S4:838-843
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K1: p' = z + beta p ; Ap = A p' ; partial (Ap,p').
 //
 // A warp owns 62 adjacent columns and marches down a segment of rows. Lane l holds columns
 // s+2l, s+2l+1 of a 64-column window [s, s+64), s = 62*warp_column: the window's first and last
 // column are the left/right neighbours of the owned range, recomputed instead of exchanged, so
-// warps never synchronise with each other. p' of rows i-1, i, i+1 lives in registers; each new
-// row costs one 16-byte load per lane from r, D, p, a, b and one 16-byte store to p', Ap.
-// The operands of row i+2 are requested before row i is computed.
+// warps never synchronise with each other.
+//
+// The operator is evaluated in flux form, which is the reference's expression tree term by term
+// (S4:526-535): Ax = -1/h1 * (Fx(i+1/2) - Fx(i-1/2)) with Fx(i+1/2) = a(i+1,j)*(p(i+1,j)-p(i,j))/h1.
+// The flux through a face is the same floating-point expression for the two cells that share the
+// face, so it is computed once: Fx(i+1/2) is carried to the next row in a register, Fy(j+1/2) is
+// passed to the neighbouring lane by shuffle. Per row a lane loads 16 bytes each of z, p, a, b and
+// stores 16 bytes each of p', Ap; the operands of row i+2 are requested before row i is computed.
 
 constexpr int K1_WARPS = 8;
 constexpr int K1_THREADS = K1_WARPS * 32;
 constexpr int K1_OWN = 62; // owned columns per warp
 
 struct K1Args {
-    const double *r, *D, *p_old, *a, *b;
+    const double *z, *p_old, *a, *b;
     double *p_new, *Ap;
     double *partials; // [nblocks]
     Ctl *ctl;
@@ -257,23 +326,57 @@ struct K1Args {
 };
 
 struct RowIn {
-    double2 r, D, q, a; // row n = i+1
-    double2 b;          // row i
+    double2 z, q, a; // row n = i+1
+    double2 b;       // row i
 };
 
-template <bool FIRST>
-__device__ __forceinline__ double2 p_update(const double2 r, const double2 D, const double2 q, const double beta) {
-    double2 z, o;
-    z.x = (D.x != 0.0) ? r.x / D.x : 0.0; // S4:559
-    z.y = (D.y != 0.0) ? r.y / D.y : 0.0;
-    if (FIRST) return z;                  // S4:830: p = z
-    o.x = z.x + beta * q.x;               // S4:675
-    o.y = z.y + beta * q.y;
-    return o;
+struct Flux {
+    double2 fx;     // Fx(i+1/2) for the lane's two columns
+    double fm, fr;  // Fy between the lane's columns, and right of its second column
+};
+
+// Fluxes of one row. SAFE: IEEE divides (coefficients or p' outside div_const's proven range).
+template <bool SAFE>
+__device__ __forceinline__ Flux row_fluxes(const double2 an, const double2 pn, const double2 pc, const double2 bc,
+                                           const double br, const double pr, const double h1, const double rh1,
+                                           const double h2, const double rh2) {
+    Flux f;
+    const double x0 = an.x * (pn.x - pc.x), x1 = an.y * (pn.y - pc.y); // S4:527
+    const double y0 = bc.y * (pc.y - pc.x), y1 = br * (pr - pc.y);     // S4:531
+    if (SAFE) {
+        f.fx.x = __ddiv_rn(x0, h1);
+        f.fx.y = __ddiv_rn(x1, h1);
+        f.fm = __ddiv_rn(y0, h2);
+        f.fr = __ddiv_rn(y1, h2);
+    } else {
+        f.fx.x = div_const_nocheck(x0, h1, rh1);
+        f.fx.y = div_const_nocheck(x1, h1, rh1);
+        f.fm = div_const_nocheck(y0, h2, rh2);
+        f.fr = div_const_nocheck(y1, h2, rh2);
+    }
+    return f;
 }
 
-template <bool FIRST>
-__global__ void __launch_bounds__(K1_THREADS) k1_kernel(const K1Args A) {
+__device__ __noinline__ Flux row_fluxes_slow(const double2 an, const double2 pn, const double2 pc, const double2 bc,
+                                             const double br, const double pr, const double h1, const double h2) {
+    return row_fluxes<true>(an, pn, pc, bc, br, pr, h1, 0.0, h2, 0.0);
+}
+
+// Branch-free predicated stores of a column pair: the full 16-byte store for lanes whose two columns are
+// both writable, 8-byte stores for the lanes at the edge of the owned range.
+__device__ __forceinline__ void st2_pred(double *ptr, const double2 v, const int both, const int only_x, const int only_y) {
+    asm volatile("{\n\t.reg .pred pb, px, py;\n\t"
+                 "setp.ne.s32 pb, %3, 0;\n\tsetp.ne.s32 px, %4, 0;\n\tsetp.ne.s32 py, %5, 0;\n\t"
+                 "@pb st.global.v2.f64 [%0], {%1, %2};\n\t"
+                 "@px st.global.f64 [%0], %1;\n\t"
+                 "@py st.global.f64 [%0+8], %2;\n\t}"
+                 :: "l"(ptr), "d"(v.x), "d"(v.y), "r"(both), "r"(only_x), "r"(only_y) : "memory");
+}
+
+// FIRST: iteration 1, p' = z (S4:830). SAFE: coefficients not verified to be in div_const's range
+// (operator entry points with caller-supplied a, b): every divide is the IEEE one.
+template <bool FIRST, bool SAFE>
+__global__ void __launch_bounds__(K1_THREADS, 2) k1_kernel(const K1Args A) {
     Ctl *ctl = A.ctl;
     if (*reinterpret_cast<volatile int *>(&ctl->done)) return;
     const Geom g = A.g;
@@ -294,62 +397,82 @@ __global__ void __launch_bounds__(K1_THREADS) k1_kernel(const K1Args A) {
         // p' is also kept up to date on the ring (it is the neighbour block's boundary value)
         const bool wr_x = (c0 <= g.ny + 1) && (lane > 0 || s == 0);
         const bool wr_y = (c0 + 1 <= g.ny + 1) && (lane < 31 || c0 + 1 == g.ny + 1);
+        const int ap_b = own_x && own_y, ap_x = own_x && !own_y, ap_y = own_y && !own_x;
+        const int pw_b = wr_x && wr_y, pw_x = wr_x && !wr_y, pw_y = wr_y && !wr_x;
+        const double mx = own_x ? 1.0 : 0.0, my = own_y ? 1.0 : 0.0; // dot-product masks (x*1.0 is exact)
         const size_t P = (size_t)g.pitch;
+        const double *zb = A.z + c0, *qb = A.p_old + c0, *ab = A.a + c0, *bb = A.b + c0;
+        double *pob = A.p_new + c0, *apb = A.Ap + c0;
 
-        auto store2 = [&](double *base, size_t off, double2 v, bool x, bool y) {
-            if (x && y) *reinterpret_cast<double2 *>(base + off) = v;
-            else if (x) base[off] = v.x;
-            else if (y) base[off + 1] = v.y;
-        };
         auto load_row = [&](int n, bool with_b) {
             RowIn in;
-            const size_t o = (size_t)n * P + c0;
-            in.r = ld2(A.r, o, ld_ok);
-            in.D = ld2(A.D, o, ld_ok);
-            in.q = FIRST ? make_double2(0.0, 0.0) : ld2(A.p_old, o, ld_ok);
-            in.a = ld2(A.a, o, ld_ok);
-            in.b = with_b ? ld2(A.b, o - P, ld_ok) : make_double2(0.0, 0.0);
+            const size_t o = (size_t)n * P;
+            in.z = ld2(zb, o, ld_ok);
+            in.q = FIRST ? make_double2(0.0, 0.0) : ld2(qb, o, ld_ok);
+            in.a = ld2(ab, o, ld_ok);
+            in.b = with_b ? ld2(bb, o - P, ld_ok) : make_double2(0.0, 0.0);
             return in;
         };
+        auto p_update = [&](const RowIn &in) {
+            if (FIRST) return in.z;
+            return make_double2(in.z.x + beta * in.q.x, in.z.y + beta * in.q.y); // S4:675
+        };
 
-        // rows i_lo-1 and i_lo
+        // rows i_lo-1 and i_lo: p' of both, and the flux through the face between them
         RowIn in = load_row(i_lo - 1, false);
-        double2 pm = p_update<FIRST>(in.r, in.D, in.q, beta);
-        if (i_lo == 1) store2(A.p_new, (size_t)0 * P + c0, pm, wr_x, wr_y); // ring row 0
+        const double2 pm = p_update(in);
+        if (i_lo == 1) st2_pred(pob, pm, pw_b, pw_x, pw_y); // ring row 0
         in = load_row(i_lo, false);
-        double2 pc = p_update<FIRST>(in.r, in.D, in.q, beta);
-        double2 ac = in.a;
-        store2(A.p_new, (size_t)i_lo * P + c0, pc, wr_x, wr_y);
+        double2 pc = p_update(in);
+        st2_pred(pob + (size_t)i_lo * P, pc, pw_b, pw_x, pw_y);
+        bool bad_c = !SAFE && !(in_div_range(pm.x) && in_div_range(pm.y) && in_div_range(pc.x) && in_div_range(pc.y));
+        double2 fxl;
+        {
+            const double x0 = in.a.x * (pc.x - pm.x), x1 = in.a.y * (pc.y - pm.y);
+            if (SAFE || __any_sync(0xffffffffu, bad_c)) {
+                fxl.x = __ddiv_rn(x0, h1);
+                fxl.y = __ddiv_rn(x1, h1);
+            } else {
+                fxl.x = div_const_nocheck(x0, h1, rh1);
+                fxl.y = div_const_nocheck(x1, h1, rh1);
+            }
+        }
+
+        // one row: consumes the operands of row i+1, leaves p'(i+1) and Fx(i+1/2) for the next call
+        auto row_step = [&](const int i, const RowIn &cur, const int st_b, const int st_x, const int st_y) {
+            const double2 pn = p_update(cur);
+            st2_pred(pob + (size_t)(i + 1) * P, pn, st_b, st_x, st_y);
+            const double pr = shfl_dn1(pc.x); // right neighbour of the lane's second column
+            const double br = shfl_dn1(cur.b.x);
+            Flux f;
+            if (SAFE) f = row_fluxes<true>(cur.a, pn, pc, cur.b, br, pr, h1, rh1, h2, rh2);
+            else {
+                const bool bad_n = !(in_div_range(pn.x) && in_div_range(pn.y));
+                if (__any_sync(0xffffffffu, bad_c | bad_n)) f = row_fluxes_slow(cur.a, pn, pc, cur.b, br, pr, h1, h2);
+                else f = row_fluxes<false>(cur.a, pn, pc, cur.b, br, pr, h1, rh1, h2, rh2);
+                bad_c = bad_n;
+            }
+            const double fl = shfl_up1(f.fr); // Fy left of the lane's first column = previous lane's right flux
+            double2 out;
+            out.x = mih1 * (f.fx.x - fxl.x) + mih2 * (f.fm - fl);   // S4:526-535
+            out.y = mih1 * (f.fx.y - fxl.y) + mih2 * (f.fr - f.fm);
+            st2_pred(apb + (size_t)i * P, out, ap_b, ap_x, ap_y);
+            acc[0] += (out.x * pc.x) * mx; // S4:594 (masked lanes add +0.0)
+            acc[0] += (out.y * pc.y) * my;
+            pc = pn;
+            fxl = f.fx;
+        };
 
         RowIn nxt = load_row(i_lo + 1, true);
-        for (int i = i_lo; i <= i_hi; ++i) {
+#pragma unroll 2
+        for (int i = i_lo; i < i_hi; ++i) {
             const RowIn cur = nxt;
-            if (i < i_hi) nxt = load_row(i + 2, true); // in flight while row i is computed
-            const double2 pn = p_update<FIRST>(cur.r, cur.D, cur.q, beta);
-            const double2 an = cur.a, bc = cur.b;
-            if (i + 1 <= i_hi || i + 1 == g.nx + 1) store2(A.p_new, (size_t)(i + 1) * P + c0, pn, wr_x, wr_y);
-
-            // j-neighbours: left of .x is the previous lane's .y, right of .y is the next lane's .x
-            const double pl = shfl_up1(pc.y);
-            const double pr = shfl_dn1(pc.x);
-            const double br = shfl_dn1(bc.x);
-            double2 out;
-            {   // S4:526-535 for column c0
-                const double ax = mih1 * (div_const(an.x * (pn.x - pc.x), h1, rh1) - div_const(ac.x * (pc.x - pm.x), h1, rh1));
-                const double ay = mih2 * (div_const(bc.y * (pc.y - pc.x), h2, rh2) - div_const(bc.x * (pc.x - pl), h2, rh2));
-                out.x = ax + ay;
-            }
-            {   // column c0+1
-                const double ax = mih1 * (div_const(an.y * (pn.y - pc.y), h1, rh1) - div_const(ac.y * (pc.y - pm.y), h1, rh1));
-                const double ay = mih2 * (div_const(br * (pr - pc.y), h2, rh2) - div_const(bc.y * (pc.y - pc.x), h2, rh2));
-                out.y = ax + ay;
-            }
-            store2(A.Ap, (size_t)i * P + c0, out, own_x, own_y);
-            if (own_x) acc[0] += out.x * pc.x; // S4:594: sum += x*y
-            if (own_y) acc[0] += out.y * pc.y;
-            pm = pc;
-            pc = pn;
-            ac = an;
+            nxt = load_row(i + 2, true); // in flight while row i is computed
+            row_step(i, cur, pw_b, pw_x, pw_y);
+        }
+        {   // last row of the segment: row i_hi+1 belongs to the next segment unless it is the ring row nx+1
+            const int last = (i_hi == g.nx);
+            row_step(i_hi, nxt, pw_b & last, pw_x & last, pw_y & last);
         }
     }
 
@@ -369,7 +492,7 @@ constexpr int K2_THREADS = 256;
 constexpr int K2_ROWS = 4; // rows per thread
 
 struct K2Args {
-    double *w, *r;
+    double *w, *r, *z;
     const double *p, *Ap, *D;
     double *partials; // [2][nblocks]
     double *trace;    // [trace_len][3] or null
@@ -409,27 +532,22 @@ __device__ __forceinline__ void finalize_iteration(Ctl *ctl, const Consts &c, do
     }
 }
 
-// MODE 0: iteration. MODE 1: initialisation -- only zr_old = (D^-1 r, r) (S4:820-843); w, r untouched.
-template <int MODE>
 __global__ void __launch_bounds__(K2_THREADS) k2_kernel(const K2Args A) {
     Ctl *ctl = A.ctl;
     if (*reinterpret_cast<volatile int *>(&ctl->done)) return;
     const Geom g = A.g;
-    double alpha = 0.0;
-    if (MODE == 0) {
-        const double denom = A.c.multi ? ctl->red[0] : ctl->denom;
-        const bool brk = (A.c.norm_mode == 1) ? (denom < 1e-15) : (fabs(denom) < 1e-15); // S0:128 | S4:876
-        if (brk) {
-            if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
-                ctl->denom = denom;
-                ctl->status = STOP_DENOM;
-                __threadfence();
-                ctl->done = 1;
-            }
-            return;
+    const double denom = A.c.multi ? ctl->red[0] : ctl->denom;
+    const bool brk = (A.c.norm_mode == 1) ? (denom < 1e-15) : (fabs(denom) < 1e-15); // S0:128 | S4:876
+    if (brk) {
+        if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
+            ctl->denom = denom;
+            ctl->status = STOP_DENOM;
+            __threadfence();
+            ctl->done = 1;
         }
-        alpha = ctl->zr_old / denom; // S4:877
+        return;
     }
+    const double alpha = ctl->zr_old / denom; // S4:877
     const int c0 = 2 * (blockIdx.x * K2_THREADS + threadIdx.x);
     const int li0 = 1 + blockIdx.y * K2_ROWS;
     const bool vx = (c0 >= 1) && (c0 <= g.ny);
@@ -444,41 +562,40 @@ __global__ void __launch_bounds__(K2_THREADS) k2_kernel(const K2Args A) {
             const size_t o = (size_t)li * g.pitch + c0;
             r[t] = ld2(A.r, o, ok);
             D[t] = ok ? __ldg(reinterpret_cast<const double2 *>(A.D + o)) : make_double2(1.0, 1.0);
-            if (MODE == 0) {
-                w[t] = ld2(A.w, o, ok);
-                p[t] = ld2(A.p, o, ok);
-                q[t] = ld2(A.Ap, o, ok);
-            }
+            w[t] = ld2(A.w, o, ok);
+            p[t] = ld2(A.p, o, ok);
+            q[t] = ld2(A.Ap, o, ok);
         }
 #pragma unroll
         for (int t = 0; t < K2_ROWS; ++t) {
             const int li = li0 + t;
             if (li > g.nx) break;
             const size_t o = (size_t)li * g.pitch + c0;
-            double2 wn = make_double2(0.0, 0.0), rn = r[t];
-            if (MODE == 0) {
-                wn.x = w[t].x + alpha * p[t].x; // S4:647
-                wn.y = w[t].y + alpha * p[t].y;
-                rn.x = r[t].x - alpha * q[t].x; // S4:648
-                rn.y = r[t].y - alpha * q[t].y;
-                const double dx = wn.x - w[t].x, dy = wn.y - w[t].y; // S4:653
-                if (vx) acc[0] += dx * dx;
-                if (vy) acc[0] += dy * dy;
-                if (vx && vy) {
-                    *reinterpret_cast<double2 *>(A.w + o) = wn;
-                    *reinterpret_cast<double2 *>(A.r + o) = rn;
-                } else if (vx) {
-                    A.w[o] = wn.x;
-                    A.r[o] = rn.x;
-                } else {
-                    A.w[o + 1] = wn.y;
-                    A.r[o + 1] = rn.y;
-                }
+            double2 wn, rn, zn;
+            wn.x = w[t].x + alpha * p[t].x; // S4:647
+            wn.y = w[t].y + alpha * p[t].y;
+            rn.x = r[t].x - alpha * q[t].x; // S4:648
+            rn.y = r[t].y - alpha * q[t].y;
+            const double dx = wn.x - w[t].x, dy = wn.y - w[t].y; // S4:653
+            zn.x = precond_div(rn.x, D[t].x); // S4:559
+            zn.y = precond_div(rn.y, D[t].y);
+            if (vx) acc[0] += dx * dx;
+            if (vy) acc[0] += dy * dy;
+            if (vx) acc[1] += zn.x * rn.x; // S4:594
+            if (vy) acc[1] += zn.y * rn.y;
+            if (vx && vy) {
+                *reinterpret_cast<double2 *>(A.w + o) = wn;
+                *reinterpret_cast<double2 *>(A.r + o) = rn;
+                *reinterpret_cast<double2 *>(A.z + o) = zn;
+            } else if (vx) {
+                A.w[o] = wn.x;
+                A.r[o] = rn.x;
+                A.z[o] = zn.x;
+            } else {
+                A.w[o + 1] = wn.y;
+                A.r[o + 1] = rn.y;
+                A.z[o + 1] = zn.y;
             }
-            const double zx = (D[t].x != 0.0) ? rn.x / D[t].x : 0.0; // S4:559
-            const double zy = (D[t].y != 0.0) ? rn.y / D[t].y : 0.0;
-            if (vx) acc[1] += zx * rn.x; // S4:594
-            if (vy) acc[1] += zy * rn.y;
         }
     }
     double tot[2];
@@ -486,10 +603,7 @@ __global__ void __launch_bounds__(K2_THREADS) k2_kernel(const K2Args A) {
         const double zr = tot[1] * A.c.h1 * A.c.h2; // S3:191
         ctl->red[1] = tot[0];
         ctl->red[2] = zr;
-        if (!A.c.multi) {
-            if (MODE == 1) ctl->zr_old = zr; // S4:838-843
-            else finalize_iteration(ctl, A.c, A.trace, alpha, tot[0], zr);
-        }
+        if (!A.c.multi) finalize_iteration(ctl, A.c, A.trace, alpha, tot[0], zr);
     }
 }
 

@@ -95,12 +95,17 @@ Consts make_consts(const pb200_params &p) {
 
 int pitch_for(int ny) { return ((ny + 2 + 15) / 16) * 16; }
 
+bool coef_in_div_range(double v) {
+    const double a = std::fabs(v);
+    return a == 0.0 || (a >= 0x1p-400 && a <= 0x1p400);
+}
+
 // ---------------------------------------------------------------------------------------------
 
 Fields::~Fields() { release(); }
 
 void Fields::release() {
-    double **all[] = {&a, &b, &D, &w, &r, &p[0], &p[1], &Ap};
+    double **all[] = {&a, &b, &D, &w, &r, &z, &p[0], &p[1], &Ap};
     for (double **q : all) {
         if (*q) cudaFree(*q);
         *q = nullptr;
@@ -110,7 +115,7 @@ void Fields::release() {
 pb200_status Fields::allocate(const Geom &geom) {
     g = geom;
     elems = static_cast<size_t>(g.nx + 2) * static_cast<size_t>(g.pitch);
-    double **all[] = {&a, &b, &D, &w, &r, &p[0], &p[1], &Ap};
+    double **all[] = {&a, &b, &D, &w, &r, &z, &p[0], &p[1], &Ap};
     for (double **q : all) CK(cudaMalloc(q, elems * sizeof(double)));
     return PB200_OK;
 }
@@ -155,6 +160,7 @@ void Solver::plan_launch() {
     k2_grid.y = (f.g.nx + K2_ROWS - 1) / K2_ROWS;
     k2_grid.z = 1;
     norms_grid = dim3((f.g.ny + 255) / 256, std::min(f.g.nx, 512), 1);
+    init_grid = dim3((f.g.pitch + INIT_THREADS - 1) / INIT_THREADS, std::min(f.g.nx + 2, 1024), 1);
 }
 
 pb200_status Solver::create(const pb200_params &params) {
@@ -184,6 +190,8 @@ pb200_status Solver::create(const pb200_params &params) {
     g.M = prm.M;
     g.N = prm.N;
     c = make_consts(prm);
+    // the coefficients are 1, 1/eps or a blend of the two (S4:167-177): div_const's fast path needs them in range
+    safe_div = !(coef_in_div_range(1.0 / c.eps) && coef_in_div_range(c.eps));
     CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     st = f.allocate(g);
     if (st != PB200_OK) return st;
@@ -191,7 +199,8 @@ pb200_status Solver::create(const pb200_params &params) {
     const size_t nb1 = static_cast<size_t>(k1_grid.x) * k1_grid.y, nb2 = static_cast<size_t>(k2_grid.x) * k2_grid.y;
     CK(cudaMalloc(&ctl, sizeof(Ctl)));
     CK(cudaMalloc(&part1, nb1 * sizeof(double)));
-    CK(cudaMalloc(&part2, 2 * std::max(nb2, static_cast<size_t>(norms_grid.x) * norms_grid.y) * sizeof(double)));
+    const size_t nb3 = std::max(static_cast<size_t>(norms_grid.x) * norms_grid.y, static_cast<size_t>(init_grid.x) * init_grid.y);
+    CK(cudaMalloc(&part2, 2 * std::max(nb2, nb3) * sizeof(double)));
     CK(cudaMalloc(&norms, 4 * sizeof(double)));
     if (c.trace_len > 0) {
         CK(cudaMalloc(&trace, static_cast<size_t>(c.trace_len) * 3 * sizeof(double)));
@@ -218,10 +227,31 @@ pb200_status Solver::run_setup() {
     return PB200_OK;
 }
 
+void Solver::launch_k1(const K1Args &a, bool first) {
+    if (first) {
+        if (safe_div) k1_kernel<true, true><<<k1_grid, K1_THREADS, 0, stream>>>(a);
+        else k1_kernel<true, false><<<k1_grid, K1_THREADS, 0, stream>>>(a);
+    } else {
+        if (safe_div) k1_kernel<false, true><<<k1_grid, K1_THREADS, 0, stream>>>(a);
+        else k1_kernel<false, false><<<k1_grid, K1_THREADS, 0, stream>>>(a);
+    }
+}
+
+void Solver::launch_init() {
+    InitArgs ia{};
+    ia.r = f.r;
+    ia.D = f.D;
+    ia.z = f.z;
+    ia.partials = part2;
+    ia.ctl = ctl;
+    ia.g = f.g;
+    ia.c = c;
+    init_kernel<<<init_grid, INIT_THREADS, 0, stream>>>(ia);
+}
+
 void Solver::launch_iteration(long long k, bool first) {
     K1Args a1{};
-    a1.r = f.r;
-    a1.D = f.D;
+    a1.z = f.z;
     a1.p_old = f.p[(k - 1) & 1];
     a1.a = f.a;
     a1.b = f.b;
@@ -232,12 +262,12 @@ void Solver::launch_iteration(long long k, bool first) {
     a1.g = f.g;
     a1.c = c;
     a1.rows_per_seg = rows_per_seg;
-    if (first) k1_kernel<true><<<k1_grid, K1_THREADS, 0, stream>>>(a1);
-    else k1_kernel<false><<<k1_grid, K1_THREADS, 0, stream>>>(a1);
+    launch_k1(a1, first);
     if (c.multi) allreduce(0, 1);
     K2Args a2{};
     a2.w = f.w;
     a2.r = f.r;
+    a2.z = f.z;
     a2.p = f.p[k & 1];
     a2.Ap = f.Ap;
     a2.D = f.D;
@@ -246,9 +276,9 @@ void Solver::launch_iteration(long long k, bool first) {
     a2.ctl = ctl;
     a2.g = f.g;
     a2.c = c;
-    k2_kernel<0><<<k2_grid, K2_THREADS, 0, stream>>>(a2);
+    k2_kernel<<<k2_grid, K2_THREADS, 0, stream>>>(a2);
     if (c.multi) {
-        exchange_r_halo();
+        exchange_z_halo();
         allreduce(1, 2);
         finalize_kernel<<<1, 1, 0, stream>>>(ctl, c, trace, 0);
     }
@@ -266,29 +296,17 @@ pb200_status Solver::solve(pb200_result *res) {
         pb200_status st = run_setup();
         if (st != PB200_OK) return st;
     }
-    // ---- init (S4:803-843): w = 0 and r = B were written by setup; zr_old = (D^-1 r, r)
+    // ---- init (S4:803-843): w = 0 and r = B were written by setup; z = D^-1 r, zr_old = (z, r)
     CK(cudaMemsetAsync(ctl, 0, sizeof(Ctl), stream));
     CK(cudaMemsetAsync(norms, 0, 4 * sizeof(double), stream));
-    {
-        K2Args a2{};
-        a2.w = f.w;
-        a2.r = f.r;
-        a2.p = f.p[0];
-        a2.Ap = f.Ap;
-        a2.D = f.D;
-        a2.partials = part2;
-        a2.ctl = ctl;
-        a2.g = f.g;
-        a2.c = c;
-        k2_kernel<1><<<k2_grid, K2_THREADS, 0, stream>>>(a2);
+    launch_init();
+    ++launches;
+    if (c.multi) {
+        allreduce(2, 1);
+        finalize_kernel<<<1, 1, 0, stream>>>(ctl, c, trace, 1);
         ++launches;
-        if (c.multi) {
-            allreduce(2, 1);
-            finalize_kernel<<<1, 1, 0, stream>>>(ctl, c, trace, 1);
-            ++launches;
-        }
-        CK(cudaGetLastError());
     }
+    CK(cudaGetLastError());
 
     // ---- loop (S4:845-943)
     const double pts_local = static_cast<double>(f.g.nx) * f.g.ny;
@@ -397,27 +415,23 @@ pb200_status Solver::profile_iteration(int iters, double ms_out[2]) {
     pb200_status st = run_setup();
     if (st != PB200_OK) return st;
     CK(cudaMemsetAsync(ctl, 0, sizeof(Ctl), stream));
-    K2Args a2{};
-    a2.w = f.w; a2.r = f.r; a2.p = f.p[0]; a2.Ap = f.Ap; a2.D = f.D; a2.partials = part2; a2.ctl = ctl; a2.g = f.g; a2.c = c;
-    a2.c.fixed = 1;
-    a2.c.max_iter = 1LL << 60;
-    k2_kernel<1><<<k2_grid, K2_THREADS, 0, stream>>>(a2);
-    std::vector<cudaEvent_t> ev(3 * (size_t)iters);
-    for (auto &e : ev) CK(cudaEventCreate(&e));
     const Consts saved = c;
     c.fixed = 1;
     c.max_iter = 1LL << 60;
+    launch_init();
+    std::vector<cudaEvent_t> ev(3 * (size_t)iters);
+    for (auto &e : ev) CK(cudaEventCreate(&e));
     for (int k = 1; k <= iters; ++k) {
         K1Args a1{};
-        a1.r = f.r; a1.D = f.D; a1.p_old = f.p[(k - 1) & 1]; a1.a = f.a; a1.b = f.b; a1.p_new = f.p[k & 1]; a1.Ap = f.Ap;
+        a1.z = f.z; a1.p_old = f.p[(k - 1) & 1]; a1.a = f.a; a1.b = f.b; a1.p_new = f.p[k & 1]; a1.Ap = f.Ap;
         a1.partials = part1; a1.ctl = ctl; a1.g = f.g; a1.c = c; a1.rows_per_seg = rows_per_seg;
-        a2.p = f.p[k & 1];
-        a2.c = c;
+        K2Args a2{};
+        a2.w = f.w; a2.r = f.r; a2.z = f.z; a2.p = f.p[k & 1]; a2.Ap = f.Ap; a2.D = f.D; a2.partials = part2; a2.ctl = ctl;
+        a2.g = f.g; a2.c = c;
         cudaEventRecord(ev[3 * (k - 1) + 0], stream);
-        if (k == 1) k1_kernel<true><<<k1_grid, K1_THREADS, 0, stream>>>(a1);
-        else k1_kernel<false><<<k1_grid, K1_THREADS, 0, stream>>>(a1);
+        launch_k1(a1, k == 1);
         cudaEventRecord(ev[3 * (k - 1) + 1], stream);
-        k2_kernel<0><<<k2_grid, K2_THREADS, 0, stream>>>(a2);
+        k2_kernel<<<k2_grid, K2_THREADS, 0, stream>>>(a2);
         cudaEventRecord(ev[3 * (k - 1) + 2], stream);
     }
     c = saved;

@@ -21,15 +21,15 @@ void choose_process_grid(int size, int &Px, int &Py);
 void decompose_2d(int M, int N, int Px, int Py, int rank, int &i0, int &i1, int &j0, int &j1);
 pb200_status validate(const pb200_params &p);
 Consts make_consts(const pb200_params &p);
+bool coef_in_div_range(double v); // zero, or 2^-400 <= |v| <= 2^400
 int pitch_for(int ny);
 
-// The eight device arrays of one block (the reference's d_a..d_Ap, S4:738-749, plus the stored
-// diagonal D and a second p for the ping-pong; no d_B: r is initialised in place, no d_z: z is
-// never stored).
+// The nine device arrays of one block (the reference's d_a..d_Ap, S4:738-749, plus the stored
+// diagonal D and a second p for the ping-pong; no d_B: r is initialised in place).
 struct Fields {
     Geom g{};
     size_t elems = 0;
-    double *a = nullptr, *b = nullptr, *D = nullptr, *w = nullptr, *r = nullptr, *p[2] = {nullptr, nullptr}, *Ap = nullptr;
+    double *a = nullptr, *b = nullptr, *D = nullptr, *w = nullptr, *r = nullptr, *z = nullptr, *p[2] = {nullptr, nullptr}, *Ap = nullptr;
     ~Fields();
     pb200_status allocate(const Geom &geom);
     void release();
@@ -49,7 +49,8 @@ struct Solver {
     double *part1 = nullptr, *part2 = nullptr, *trace = nullptr, *norms = nullptr;
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr, ev_call0 = nullptr, ev_call1 = nullptr, ev_poll[2] = {nullptr, nullptr};
     cudaGraphExec_t graph_exec = nullptr;
-    dim3 k1_grid, k2_grid, norms_grid;
+    dim3 k1_grid, k2_grid, norms_grid, init_grid;
+    bool safe_div = false; // coefficients outside div_const's verified range: IEEE divides everywhere
     int rows_per_seg = 32;
     long long launches = 0;
     long long last_iter = 0;
@@ -62,6 +63,8 @@ struct Solver {
     pb200_status run_setup();
     void plan_launch();
     void launch_iteration(long long k, bool first);
+    void launch_k1(const K1Args &a, bool first);
+    void launch_init();
     int kernels_per_iteration() const;
     pb200_status solve(pb200_result *res);
     pb200_status profile_iteration(int iters, double ms_out[2]);
@@ -73,7 +76,7 @@ struct Solver {
     bool comm_ready() const;
     void destroy_comm();
     void allreduce(int first, int count); // in place on ctl->red[first .. first+count)
-    void exchange_r_halo();               // boundary rows/columns of r -> neighbours' ring
+    void exchange_z_halo();               // boundary rows/columns of z -> neighbours' ring
     int halo_kernels_per_iteration() const;
     pb200_status reduce_norms_host(double h_norms[4]);
 };

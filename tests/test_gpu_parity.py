@@ -95,6 +95,24 @@ def test_apply_A_random_coefficients(oracle):
     assert np.array_equal(got, oracle.apply_A(p, a, b, h1, h2))
 
 
+@pytest.mark.parametrize("pscale,ascale", [(1e-250, 1.0), (1e-310, 1.0), (1e250, 1e-3), (1.0, 1e200), (1e-150, 1e-160),
+                                           (1.0, 1e-300)])
+def test_apply_A_extreme_magnitudes(oracle, pscale, ascale):
+    """Outside the range where the fast constant-divisor division is proven, the kernel must switch to IEEE
+    divides (per row for tiny/huge p, for the whole launch for out-of-range coefficients): still bit-exact."""
+    nx, ny = 37, 130
+    h1, h2 = steps(nx + 1, ny + 1)
+    a = (np.abs(seeded_field(nx, ny, seed=1)) + 0.5) * ascale
+    b = (np.abs(seeded_field(nx, ny, seed=2)) + 0.5) * ascale
+    p = seeded_field(nx, ny, seed=3)
+    p[5:20, 3:90] *= pscale          # a patch of extreme values next to ordinary ones
+    p[25, :] = 0.0
+    with np.errstate(over="ignore", under="ignore", invalid="ignore"):
+        want = oracle.apply_A(p, a, b, h1, h2)
+    got = pb.op_apply_A(pb.default_params(nx + 1, ny + 1), p, a, b)
+    assert np.array_equal(got, want, equal_nan=True)
+
+
 def test_apply_A_against_reference_fixture(golden_arrays):
     p = seeded_field(39, 39, seed=1234)
     got = pb.op_apply_A(pb.default_params(40, 40), p, golden_arrays["a_full40"], golden_arrays["b_full40"])
