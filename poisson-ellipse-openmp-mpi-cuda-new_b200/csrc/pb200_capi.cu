@@ -111,7 +111,7 @@ struct OpBlock {
     }
     pb200_status diag() {
         dim3 grid((f.g.pitch + 255) / 256, f.g.nx + 2);
-        diag_kernel<<<grid, 256>>>(f.g, c, f.a, f.b, f.D);
+        diag_kernel<<<grid, 256>>>(f.g, c, f.a, f.b, f.D, f.cls);
         CK(cudaGetLastError());
         return PB200_OK;
     }
@@ -134,6 +134,7 @@ struct OpBlock {
         a.p_old = p_old;
         a.a = f.a;
         a.b = f.b;
+        a.cls = f.cls;
         a.p_new = p_new;
         a.Ap = f.Ap;
         a.partials = part;
@@ -159,6 +160,7 @@ struct OpBlock {
         a.p = p;
         a.Ap = f.Ap;
         a.D = f.D;
+        a.cls = f.cls;
         a.partials = part;
         a.ctl = ctl;
         a.g = f.g;
@@ -328,7 +330,7 @@ pb200_status pb200_op_setup(const pb200_params *p, int32_t i0, int32_t i1, int32
     OpBlock ob;
     TRY(ob.init(*p, i1 - i0 + 1, j1 - j0 + 1, i0 - 1, j0 - 1));
     dim3 grid((ob.f.g.pitch + 255) / 256, ob.f.g.nx + 2);
-    setup_kernel<<<grid, 256>>>(ob.f.g, ob.c, ob.f.a, ob.f.b, ob.f.D, ob.f.r, nullptr, nullptr, nullptr, nullptr);
+    setup_kernel<<<grid, 256>>>(ob.f.g, ob.c, ob.f.a, ob.f.b, ob.f.D, ob.f.r, nullptr, nullptr, nullptr, nullptr, ob.f.cls);
     CK(cudaGetLastError());
     CK(cudaDeviceSynchronize());
     if (a) TRY(ob.get_all(a, ob.f.a));
@@ -348,6 +350,7 @@ pb200_status pb200_op_apply_A(const pb200_params *p, const double *pvec, const d
     TRY(ob.put(ob.f.b, b));
     ob.scan_coefficients(a);
     ob.scan_coefficients(b);
+    TRY(ob.diag()); // classifies the caller's coefficients
     // z = 0, beta = 1: K1 forms p' = 0 + 1*p = p exactly, then Ap = A p'
     TRY(ob.set_ctl(1.0, 0.0));
     TRY(ob.k1(false, ob.f.p[0], ob.f.p[1]));

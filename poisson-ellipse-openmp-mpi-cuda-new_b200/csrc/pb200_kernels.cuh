@@ -43,7 +43,27 @@ struct Consts {
     int multi;                 // 1: scalars are all-reduced between kernels, finalize runs separately
     int trace_len;
     long long max_iter;        // S4:1007 (or fixed_iters): enforced on the device
+    // Coefficient classes: a, b are 1.0 (class 0) or 1/eps (class 1) everywhere except on the
+    // O(M+N) cells whose edge is cut by the ellipse (class 2: value kept in the full array). The diagonal
+    // D = (a+a)/(h1*h1) + (b+b)/(h2*h2) then takes one of 9 values: lutD[3*na+nb], na/nb = how many of the
+    // two a's / b's are 1/eps; lutR = RN(1/lutD). Class 15 = anything else (value kept in the full array).
+    double lutD[16], lutR[16];
 };
+
+constexpr unsigned CLS_GENERAL = 2u;  // a / b class: read the full array
+constexpr unsigned DCLS_GENERAL = 15u; // D class: read the full array
+
+// class byte of one cell: bits 0-1 a class, bits 2-3 b class, bits 4-7 D class
+__device__ __forceinline__ unsigned coef_class(double v, double inv_eps) {
+    return (v == 1.0) ? 0u : ((v == inv_eps) ? 1u : CLS_GENERAL);
+}
+__device__ __forceinline__ unsigned diag_class(const Consts &c, unsigned ca_ip, unsigned ca, unsigned cb_jp, unsigned cb, double vD) {
+    if (ca_ip < 2u && ca < 2u && cb_jp < 2u && cb < 2u) {
+        const unsigned idx = (ca_ip + ca) * 3u + (cb_jp + cb);
+        if (c.lutD[idx] == vD) return idx;
+    }
+    return DCLS_GENERAL;
+}
 
 // Device-resident loop state: what the reference keeps in host variables (S4:836-848, 872-932).
 struct Ctl {
@@ -194,22 +214,30 @@ __device__ __forceinline__ double coef_b(const Consts &c, int gi, int gj) { // S
 __global__ void __launch_bounds__(256) setup_kernel(Geom g, Consts c, double *__restrict__ a, double *__restrict__ b,
                                                     double *__restrict__ D, double *__restrict__ r,
                                                     double *__restrict__ w, double *__restrict__ p0,
-                                                    double *__restrict__ p1, double *__restrict__ Ap) {
+                                                    double *__restrict__ p1, double *__restrict__ Ap,
+                                                    unsigned char *__restrict__ cls) {
     const int lj = blockIdx.x * blockDim.x + threadIdx.x;
     const int li = blockIdx.y;
     if (lj >= g.pitch) return;
     const size_t o = (size_t)li * g.pitch + lj;
     double va = 0.0, vb = 0.0, vD = 1.0, vr = 0.0;
+    unsigned vc = CLS_GENERAL | (CLS_GENERAL << 2) | (DCLS_GENERAL << 4);
     if (lj <= g.ny + 1) {
         const int gi = g.gi0 + li, gj = g.gj0 + lj;
         va = coef_a(c, gi, gj);
         vb = coef_b(c, gi, gj);
+        const unsigned ca = coef_class(va, c.inv_eps), cb = coef_class(vb, c.inv_eps);
+        unsigned cD = DCLS_GENERAL;
         if (gi >= 1 && gi <= g.M - 1 && gj >= 1 && gj <= g.N - 1) {
             const double x = c.A1 + gi * c.h1, y = c.A2 + gj * c.h2;
             vr = (x * x + c.ell_c * y * y < 1.0) ? c.f_val : 0.0; // S4:32-34, 189
-            vD = (coef_a(c, gi + 1, gj) + va) / c.h1h1 + (coef_b(c, gi, gj + 1) + vb) / c.h2h2; // S4:556-557
+            const double a_ip = coef_a(c, gi + 1, gj), b_jp = coef_b(c, gi, gj + 1);
+            vD = (a_ip + va) / c.h1h1 + (b_jp + vb) / c.h2h2; // S4:556-557
+            cD = diag_class(c, coef_class(a_ip, c.inv_eps), ca, coef_class(b_jp, c.inv_eps), cb, vD);
         }
+        vc = ca | (cb << 2) | (cD << 4);
     }
+    if (cls) cls[o] = (unsigned char)vc;
     a[o] = va;
     b[o] = vb;
     D[o] = vD;
@@ -222,15 +250,26 @@ __global__ void __launch_bounds__(256) setup_kernel(Geom g, Consts c, double *__
 
 // D from caller-supplied a, b (operator entry points only: the solver's D comes from setup_kernel).
 __global__ void __launch_bounds__(256) diag_kernel(Geom g, Consts c, const double *__restrict__ a,
-                                                   const double *__restrict__ b, double *__restrict__ D) {
+                                                   const double *__restrict__ b, double *__restrict__ D,
+                                                   unsigned char *__restrict__ cls) {
     const int lj = blockIdx.x * blockDim.x + threadIdx.x;
     const int li = blockIdx.y;
     if (lj >= g.pitch) return;
     const size_t o = (size_t)li * g.pitch + lj;
     double vD = 1.0;
-    if (li >= 1 && li <= g.nx && lj >= 1 && lj <= g.ny)
-        vD = (a[o + g.pitch] + a[o]) / c.h1h1 + (b[o + 1] + b[o]) / c.h2h2;
+    unsigned vc = CLS_GENERAL | (CLS_GENERAL << 2) | (DCLS_GENERAL << 4);
+    if (lj <= g.ny + 1) {
+        const unsigned ca = coef_class(a[o], c.inv_eps), cb = coef_class(b[o], c.inv_eps);
+        unsigned cD = DCLS_GENERAL;
+        if (li >= 1 && li <= g.nx && lj >= 1 && lj <= g.ny) {
+            const double a_ip = a[o + g.pitch], b_jp = b[o + 1];
+            vD = (a_ip + a[o]) / c.h1h1 + (b_jp + b[o]) / c.h2h2;
+            cD = diag_class(c, coef_class(a_ip, c.inv_eps), ca, coef_class(b_jp, c.inv_eps), cb, vD);
+        }
+        vc = ca | (cb << 2) | (cD << 4);
+    }
     D[o] = vD;
+    cls[o] = (unsigned char)vc;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -308,15 +347,18 @@ __global__ void __launch_bounds__(INIT_THREADS) init_kernel(const InitArgs A) {
 // (S4:526-535): Ax = -1/h1 * (Fx(i+1/2) - Fx(i-1/2)) with Fx(i+1/2) = a(i+1,j)*(p(i+1,j)-p(i,j))/h1.
 // The flux through a face is the same floating-point expression for the two cells that share the
 // face, so it is computed once: Fx(i+1/2) is carried to the next row in a register, Fy(j+1/2) is
-// passed to the neighbouring lane by shuffle. Per row a lane loads 16 bytes each of z, p, a, b and
-// stores 16 bytes each of p', Ap; the operands of row i+2 are requested before row i is computed.
+// passed to the neighbouring lane by shuffle. Per row a lane loads 16 bytes each of z and p plus the
+// 2 class bytes of its cells (a and b are decoded from the class; the full arrays are touched only on
+// the cells the ellipse cuts) and stores 16 bytes each of p', Ap; the operands of row i+2 are requested
+// before row i is computed.
 
 constexpr int K1_WARPS = 8;
 constexpr int K1_THREADS = K1_WARPS * 32;
 constexpr int K1_OWN = 62; // owned columns per warp
 
 struct K1Args {
-    const double *z, *p_old, *a, *b;
+    const double *z, *p_old, *a, *b; // a, b: full arrays, read only where the class says "general"
+    const unsigned char *cls;
     double *p_new, *Ap;
     double *partials; // [nblocks]
     Ctl *ctl;
@@ -326,9 +368,11 @@ struct K1Args {
 };
 
 struct RowIn {
-    double2 z, q, a; // row n = i+1
-    double2 b;       // row i
+    double2 z, q;  // row n = i+1
+    unsigned cls;  // class bytes of the lane's two columns in row n (low byte = first column)
 };
+
+__device__ __forceinline__ double class_value(unsigned k, double inv_eps) { return (k & 1u) ? inv_eps : 1.0; }
 
 struct Flux {
     double2 fx;     // Fx(i+1/2) for the lane's two columns
@@ -402,33 +446,45 @@ __global__ void __launch_bounds__(K1_THREADS, 2) k1_kernel(const K1Args A) {
         const double mx = own_x ? 1.0 : 0.0, my = own_y ? 1.0 : 0.0; // dot-product masks (x*1.0 is exact)
         const size_t P = (size_t)g.pitch;
         const double *zb = A.z + c0, *qb = A.p_old + c0, *ab = A.a + c0, *bb = A.b + c0;
+        const unsigned char *cb = A.cls + c0;
         double *pob = A.p_new + c0, *apb = A.Ap + c0;
+        const double inv_eps = A.c.inv_eps;
 
-        auto load_row = [&](int n, bool with_b) {
+        auto load_row = [&](int n) {
             RowIn in;
             const size_t o = (size_t)n * P;
             in.z = ld2(zb, o, ld_ok);
             in.q = FIRST ? make_double2(0.0, 0.0) : ld2(qb, o, ld_ok);
-            in.a = ld2(ab, o, ld_ok);
-            in.b = with_b ? ld2(bb, o - P, ld_ok) : make_double2(0.0, 0.0);
+            in.cls = ld_ok ? (unsigned)__ldg(reinterpret_cast<const unsigned short *>(cb + o)) : 0u;
             return in;
         };
         auto p_update = [&](const RowIn &in) {
             if (FIRST) return in.z;
             return make_double2(in.z.x + beta * in.q.x, in.z.y + beta * in.q.y); // S4:675
         };
+        // a of the lane's two columns in row n, from the class bytes (general cells: the full array)
+        auto decode_a = [&](unsigned cls, int n) {
+            double2 a = make_double2(class_value(cls, inv_eps), class_value(cls >> 8, inv_eps));
+            if (__any_sync(0xffffffffu, (cls & 0x0202u) != 0u)) {
+                if (cls & 0x0002u) a.x = __ldg(ab + (size_t)n * P);
+                if (cls & 0x0200u) a.y = __ldg(ab + (size_t)n * P + 1);
+            }
+            return a;
+        };
 
         // rows i_lo-1 and i_lo: p' of both, and the flux through the face between them
-        RowIn in = load_row(i_lo - 1, false);
+        RowIn in = load_row(i_lo - 1);
         const double2 pm = p_update(in);
         if (i_lo == 1) st2_pred(pob, pm, pw_b, pw_x, pw_y); // ring row 0
-        in = load_row(i_lo, false);
+        in = load_row(i_lo);
         double2 pc = p_update(in);
+        unsigned cls_c = in.cls;
         st2_pred(pob + (size_t)i_lo * P, pc, pw_b, pw_x, pw_y);
         bool bad_c = !SAFE && !(in_div_range(pm.x) && in_div_range(pm.y) && in_div_range(pc.x) && in_div_range(pc.y));
         double2 fxl;
         {
-            const double x0 = in.a.x * (pc.x - pm.x), x1 = in.a.y * (pc.y - pm.y);
+            const double2 ac = decode_a(cls_c, i_lo);
+            const double x0 = ac.x * (pc.x - pm.x), x1 = ac.y * (pc.y - pm.y);
             if (SAFE || __any_sync(0xffffffffu, bad_c)) {
                 fxl.x = __ddiv_rn(x0, h1);
                 fxl.y = __ddiv_rn(x1, h1);
@@ -438,18 +494,29 @@ __global__ void __launch_bounds__(K1_THREADS, 2) k1_kernel(const K1Args A) {
             }
         }
 
-        // one row: consumes the operands of row i+1, leaves p'(i+1) and Fx(i+1/2) for the next call
+        // one row: consumes the operands of row i+1, leaves p'(i+1), Fx(i+1/2) and the classes of row i+1
         auto row_step = [&](const int i, const RowIn &cur, const int st_b, const int st_x, const int st_y) {
             const double2 pn = p_update(cur);
             st2_pred(pob + (size_t)(i + 1) * P, pn, st_b, st_x, st_y);
             const double pr = shfl_dn1(pc.x); // right neighbour of the lane's second column
-            const double br = shfl_dn1(cur.b.x);
+            const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
+            double2 an = make_double2(class_value(cur.cls, inv_eps), class_value(cur.cls >> 8, inv_eps));
+            double2 bc = make_double2(class_value(cls_c >> 2, inv_eps), class_value(cls_c >> 10, inv_eps));
+            double br = class_value(cls_r >> 2, inv_eps);
+            const unsigned general = (cur.cls & 0x0202u) | (cls_c & 0x0808u) | ((lane < 31) ? (cls_r & 0x0008u) : 0u);
+            if (__any_sync(0xffffffffu, general != 0u)) { // a cell cut by the ellipse: exact values from the full arrays
+                if (cur.cls & 0x0002u) an.x = __ldg(ab + (size_t)(i + 1) * P);
+                if (cur.cls & 0x0200u) an.y = __ldg(ab + (size_t)(i + 1) * P + 1);
+                if (cls_c & 0x0008u) bc.x = __ldg(bb + (size_t)i * P);
+                if (cls_c & 0x0800u) bc.y = __ldg(bb + (size_t)i * P + 1);
+                if ((lane < 31) && (cls_r & 0x0008u)) br = __ldg(bb + (size_t)i * P + 2);
+            }
             Flux f;
-            if (SAFE) f = row_fluxes<true>(cur.a, pn, pc, cur.b, br, pr, h1, rh1, h2, rh2);
+            if (SAFE) f = row_fluxes<true>(an, pn, pc, bc, br, pr, h1, rh1, h2, rh2);
             else {
                 const bool bad_n = !(in_div_range(pn.x) && in_div_range(pn.y));
-                if (__any_sync(0xffffffffu, bad_c | bad_n)) f = row_fluxes_slow(cur.a, pn, pc, cur.b, br, pr, h1, h2);
-                else f = row_fluxes<false>(cur.a, pn, pc, cur.b, br, pr, h1, rh1, h2, rh2);
+                if (__any_sync(0xffffffffu, bad_c | bad_n)) f = row_fluxes_slow(an, pn, pc, bc, br, pr, h1, h2);
+                else f = row_fluxes<false>(an, pn, pc, bc, br, pr, h1, rh1, h2, rh2);
                 bad_c = bad_n;
             }
             const double fl = shfl_up1(f.fr); // Fy left of the lane's first column = previous lane's right flux
@@ -461,13 +528,14 @@ __global__ void __launch_bounds__(K1_THREADS, 2) k1_kernel(const K1Args A) {
             acc[0] += (out.y * pc.y) * my;
             pc = pn;
             fxl = f.fx;
+            cls_c = cur.cls;
         };
 
-        RowIn nxt = load_row(i_lo + 1, true);
+        RowIn nxt = load_row(i_lo + 1);
 #pragma unroll 2
         for (int i = i_lo; i < i_hi; ++i) {
             const RowIn cur = nxt;
-            nxt = load_row(i + 2, true); // in flight while row i is computed
+            nxt = load_row(i + 2); // in flight while row i is computed
             row_step(i, cur, pw_b, pw_x, pw_y);
         }
         {   // last row of the segment: row i_hi+1 belongs to the next segment unless it is the ring row nx+1
@@ -493,7 +561,8 @@ constexpr int K2_ROWS = 4; // rows per thread
 
 struct K2Args {
     double *w, *r, *z;
-    const double *p, *Ap, *D;
+    const double *p, *Ap, *D; // D: full array, read only where the class says "general"
+    const unsigned char *cls;
     double *partials; // [2][nblocks]
     double *trace;    // [trace_len][3] or null
     Ctl *ctl;
@@ -532,9 +601,19 @@ __device__ __forceinline__ void finalize_iteration(Ctl *ctl, const Consts &c, do
     }
 }
 
+// r / D for a diagonal taken from the class table: D and RN(1/D) are known, so the quotient is two exact-residual
+// corrections of r*RN(1/D) (see div_const); IEEE divide when r is outside the proven range.
+__device__ __forceinline__ double lut_div(double r, double2 DR) {
+    const double q = div_const_nocheck(r, DR.x, DR.y);
+    return in_div_range(r) ? q : precond_div(r, DR.x);
+}
+
 __global__ void __launch_bounds__(K2_THREADS) k2_kernel(const K2Args A) {
     Ctl *ctl = A.ctl;
+    __shared__ double2 s_lut[16];
     if (*reinterpret_cast<volatile int *>(&ctl->done)) return;
+    if (threadIdx.x < 16) s_lut[threadIdx.x] = make_double2(A.c.lutD[threadIdx.x], A.c.lutR[threadIdx.x]);
+    __syncthreads();
     const Geom g = A.g;
     const double denom = A.c.multi ? ctl->red[0] : ctl->denom;
     const bool brk = (A.c.norm_mode == 1) ? (denom < 1e-15) : (fabs(denom) < 1e-15); // S0:128 | S4:876
@@ -554,14 +633,15 @@ __global__ void __launch_bounds__(K2_THREADS) k2_kernel(const K2Args A) {
     const bool vy = (c0 + 1 <= g.ny);
     double acc[2] = {0.0, 0.0};
     if (vx || vy) {
-        double2 w[K2_ROWS], r[K2_ROWS], p[K2_ROWS], q[K2_ROWS], D[K2_ROWS];
+        double2 w[K2_ROWS], r[K2_ROWS], p[K2_ROWS], q[K2_ROWS];
+        unsigned cl[K2_ROWS];
 #pragma unroll
         for (int t = 0; t < K2_ROWS; ++t) {
             const int li = li0 + t;
             const bool ok = li <= g.nx;
             const size_t o = (size_t)li * g.pitch + c0;
             r[t] = ld2(A.r, o, ok);
-            D[t] = ok ? __ldg(reinterpret_cast<const double2 *>(A.D + o)) : make_double2(1.0, 1.0);
+            cl[t] = ok ? (unsigned)__ldg(reinterpret_cast<const unsigned short *>(A.cls + o)) : 0u;
             w[t] = ld2(A.w, o, ok);
             p[t] = ld2(A.p, o, ok);
             q[t] = ld2(A.Ap, o, ok);
@@ -577,8 +657,11 @@ __global__ void __launch_bounds__(K2_THREADS) k2_kernel(const K2Args A) {
             rn.x = r[t].x - alpha * q[t].x; // S4:648
             rn.y = r[t].y - alpha * q[t].y;
             const double dx = wn.x - w[t].x, dy = wn.y - w[t].y; // S4:653
-            zn.x = precond_div(rn.x, D[t].x); // S4:559
-            zn.y = precond_div(rn.y, D[t].y);
+            const unsigned kx = (cl[t] >> 4) & 15u, ky = (cl[t] >> 12) & 15u;
+            zn.x = lut_div(rn.x, s_lut[kx]); // S4:559
+            zn.y = lut_div(rn.y, s_lut[ky]);
+            if (kx == DCLS_GENERAL) zn.x = precond_div(rn.x, __ldg(A.D + o)); // a cell next to the ellipse boundary
+            if (ky == DCLS_GENERAL) zn.y = precond_div(rn.y, __ldg(A.D + o + 1));
             if (vx) acc[0] += dx * dx;
             if (vy) acc[0] += dy * dy;
             if (vx) acc[1] += zn.x * rn.x; // S4:594

@@ -88,6 +88,15 @@ Consts make_consts(const pb200_params &p) {
     c.fixed = p.fixed_iters > 0;
     c.multi = p.nranks > 1;
     c.trace_len = std::max(0, p.trace_len);
+    // diagonal classes: (a_ip + a_c) / (h1*h1) + (b_jp + b_c) / (h2*h2) with each coefficient 1.0 or 1/eps (S4:556-557)
+    const double pair[3] = {1.0 + 1.0, c.inv_eps + 1.0, c.inv_eps + c.inv_eps};
+    for (int na = 0; na < 3; ++na)
+        for (int nb = 0; nb < 3; ++nb) {
+            const double D = pair[na] / c.h1h1 + pair[nb] / c.h2h2;
+            c.lutD[3 * na + nb] = D;
+            c.lutR[3 * na + nb] = 1.0 / D;
+        }
+    for (int k = 9; k < 16; ++k) c.lutD[k] = c.lutR[k] = 1.0;
     const long long dflt = static_cast<long long>(p.M - 1) * static_cast<long long>(p.N - 1); // S4:1007
     c.max_iter = p.fixed_iters > 0 ? p.fixed_iters : (p.max_iter > 0 ? p.max_iter : dflt);
     return c;
@@ -110,6 +119,8 @@ void Fields::release() {
         if (*q) cudaFree(*q);
         *q = nullptr;
     }
+    if (cls) cudaFree(cls);
+    cls = nullptr;
 }
 
 pb200_status Fields::allocate(const Geom &geom) {
@@ -117,6 +128,7 @@ pb200_status Fields::allocate(const Geom &geom) {
     elems = static_cast<size_t>(g.nx + 2) * static_cast<size_t>(g.pitch);
     double **all[] = {&a, &b, &D, &w, &r, &z, &p[0], &p[1], &Ap};
     for (double **q : all) CK(cudaMalloc(q, elems * sizeof(double)));
+    CK(cudaMalloc(&cls, elems));
     return PB200_OK;
 }
 
@@ -221,7 +233,7 @@ pb200_status Solver::create(const pb200_params &params) {
 
 pb200_status Solver::run_setup() {
     dim3 grid((f.g.pitch + 255) / 256, f.g.nx + 2);
-    setup_kernel<<<grid, 256, 0, stream>>>(f.g, c, f.a, f.b, f.D, f.r, f.w, f.p[0], f.p[1], f.Ap);
+    setup_kernel<<<grid, 256, 0, stream>>>(f.g, c, f.a, f.b, f.D, f.r, f.w, f.p[0], f.p[1], f.Ap, f.cls);
     ++launches;
     CK(cudaGetLastError());
     return PB200_OK;
@@ -255,6 +267,7 @@ void Solver::launch_iteration(long long k, bool first) {
     a1.p_old = f.p[(k - 1) & 1];
     a1.a = f.a;
     a1.b = f.b;
+    a1.cls = f.cls;
     a1.p_new = f.p[k & 1];
     a1.Ap = f.Ap;
     a1.partials = part1;
@@ -271,6 +284,7 @@ void Solver::launch_iteration(long long k, bool first) {
     a2.p = f.p[k & 1];
     a2.Ap = f.Ap;
     a2.D = f.D;
+    a2.cls = f.cls;
     a2.partials = part2;
     a2.trace = trace;
     a2.ctl = ctl;
@@ -423,10 +437,10 @@ pb200_status Solver::profile_iteration(int iters, double ms_out[2]) {
     for (auto &e : ev) CK(cudaEventCreate(&e));
     for (int k = 1; k <= iters; ++k) {
         K1Args a1{};
-        a1.z = f.z; a1.p_old = f.p[(k - 1) & 1]; a1.a = f.a; a1.b = f.b; a1.p_new = f.p[k & 1]; a1.Ap = f.Ap;
+        a1.z = f.z; a1.p_old = f.p[(k - 1) & 1]; a1.a = f.a; a1.b = f.b; a1.cls = f.cls; a1.p_new = f.p[k & 1]; a1.Ap = f.Ap;
         a1.partials = part1; a1.ctl = ctl; a1.g = f.g; a1.c = c; a1.rows_per_seg = rows_per_seg;
         K2Args a2{};
-        a2.w = f.w; a2.r = f.r; a2.z = f.z; a2.p = f.p[k & 1]; a2.Ap = f.Ap; a2.D = f.D; a2.partials = part2; a2.ctl = ctl;
+        a2.w = f.w; a2.r = f.r; a2.z = f.z; a2.p = f.p[k & 1]; a2.Ap = f.Ap; a2.D = f.D; a2.cls = f.cls; a2.partials = part2; a2.ctl = ctl;
         a2.g = f.g; a2.c = c;
         cudaEventRecord(ev[3 * (k - 1) + 0], stream);
         launch_k1(a1, k == 1);

@@ -30,6 +30,7 @@ struct Fields {
     Geom g{};
     size_t elems = 0;
     double *a = nullptr, *b = nullptr, *D = nullptr, *w = nullptr, *r = nullptr, *z = nullptr, *p[2] = {nullptr, nullptr}, *Ap = nullptr;
+    unsigned char *cls = nullptr; // one class byte per stored cell (pb200_kernels.cuh)
     ~Fields();
     pb200_status allocate(const Geom &geom);
     void release();

@@ -36,6 +36,18 @@ def test_div_const_is_ieee_division(h):
     assert pb.selftest_div(h, n=1 << 21, seed=20260711) == 0
 
 
+@pytest.mark.parametrize("m,n", [(40, 40), (400, 600), (2400, 3200), (8192, 8192), (32768, 32768), (37, 53)])
+def test_class_table_diagonals_divide_exactly(m, n):
+    """K2 divides by the nine class values of the diagonal D with the same two-correction scheme."""
+    h1, h2 = steps(m, n)
+    inv_eps = 1.0 / (max(h1, h2) * max(h1, h2))
+    pair = (1.0 + 1.0, inv_eps + 1.0, inv_eps + inv_eps)
+    for na in range(3):
+        for nb in range(3):
+            D = pair[na] / (h1 * h1) + pair[nb] / (h2 * h2)
+            assert pb.selftest_div(D, n=1 << 18, seed=7 + 3 * na + nb) == 0
+
+
 # --------------------------------------------------------------------------------------------
 # coefficient / RHS / diagonal kernel
 
