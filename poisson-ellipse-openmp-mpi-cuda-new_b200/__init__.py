@@ -13,7 +13,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libpoisson_b200.so")
+LIB_PATH = os.environ.get("PB200_LIB") or os.path.join(HERE, "libpoisson_b200.so")  # PB200_LIB: tuning variants
 CLI_PATH = os.path.join(HERE, "poisson_b200")
 
 NORM_WEIGHTED, NORM_STAGE0 = 0, 1

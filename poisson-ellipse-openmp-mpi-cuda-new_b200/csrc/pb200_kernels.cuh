@@ -355,6 +355,14 @@ __global__ void __launch_bounds__(INIT_THREADS) init_kernel(const InitArgs A) {
 constexpr int K1_WARPS = 8;
 constexpr int K1_THREADS = K1_WARPS * 32;
 constexpr int K1_OWN = 62; // owned columns per warp
+#ifndef PB200_K1_MINB
+#define PB200_K1_MINB 4 // resident CTAs per SM the register allocation is held to (tuned: see DESIGN.md)
+#endif
+#ifndef PB200_K1_UNROLL
+#define PB200_K1_UNROLL 1
+#endif
+constexpr int K1_MIN_CTAS = PB200_K1_MINB;
+constexpr int K1_UNROLL = PB200_K1_UNROLL;
 
 struct K1Args {
     const double *z, *p_old, *a, *b; // a, b: full arrays, read only where the class says "general"
@@ -420,7 +428,7 @@ __device__ __forceinline__ void st2_pred(double *ptr, const double2 v, const int
 // FIRST: iteration 1, p' = z (S4:830). SAFE: coefficients not verified to be in div_const's range
 // (operator entry points with caller-supplied a, b): every divide is the IEEE one.
 template <bool FIRST, bool SAFE>
-__global__ void __launch_bounds__(K1_THREADS, 2) k1_kernel(const K1Args A) {
+__global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1Args A) {
     Ctl *ctl = A.ctl;
     if (*reinterpret_cast<volatile int *>(&ctl->done)) return;
     const Geom g = A.g;
@@ -531,17 +539,18 @@ __global__ void __launch_bounds__(K1_THREADS, 2) k1_kernel(const K1Args A) {
             cls_c = cur.cls;
         };
 
+        // The operands of row i+2 are requested before row i is computed. Deeper software prefetch does not
+        // pay (measured): a warp has six scoreboard slots, so waiting for the oldest row also waits for newer
+        // ones; latency is hidden by running many warps per SM instead (K1_MIN_CTAS).
+        const int last = (i_hi == g.nx); // row i_hi+1 belongs to the next segment unless it is the ring row nx+1
         RowIn nxt = load_row(i_lo + 1);
-#pragma unroll 2
+#pragma unroll K1_UNROLL
         for (int i = i_lo; i < i_hi; ++i) {
             const RowIn cur = nxt;
-            nxt = load_row(i + 2); // in flight while row i is computed
+            nxt = load_row(i + 2);
             row_step(i, cur, pw_b, pw_x, pw_y);
         }
-        {   // last row of the segment: row i_hi+1 belongs to the next segment unless it is the ring row nx+1
-            const int last = (i_hi == g.nx);
-            row_step(i_hi, nxt, pw_b & last, pw_x & last, pw_y & last);
-        }
+        row_step(i_hi, nxt, pw_b & last, pw_x & last, pw_y & last);
     }
 
     double tot[1];
