@@ -330,7 +330,9 @@ pb200_status Solver::solve(pb200_result *res) {
         check = static_cast<int>(std::min(64.0, std::max(2.0, 250e-6 / t_it)));
     }
     check += check & 1; // even: graph replays cover two iterations
-    const bool use_graph = prm.use_graph != 0;
+    // Graph replay is single-GPU only: with NCCL collectives captured in the graph the replay hung on this
+    // stack (NCCL 2.27.3 / driver 580, 2 ranks); multi-GPU iterations are launched directly.
+    const bool use_graph = prm.use_graph != 0 && !c.multi;
     CK(cudaEventRecord(ev_start, stream));
     long long k = 1;
     launch_iteration(k, true); // iteration 1: p = z (S4:830)

@@ -18,7 +18,7 @@ def run_cli(tmp_path, M, N, gpus, extra=()):
     dump = tmp_path / f"w_{M}x{N}_{gpus}.npy"
     js = tmp_path / f"r_{M}x{N}_{gpus}.json"
     cmd = [pb.CLI_PATH, str(M), str(N), "--gpus", str(gpus), "--dump", str(dump), "--json", str(js), *extra]
-    out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=120)
     assert out.returncode == 0, out.stderr
     return out.stdout, json.load(open(js)), np.load(dump)
 
