@@ -125,7 +125,7 @@ pb200_status pb200_get_solution(pb200_solver *s, double *host, int64_t ld);
 /* Copies min(n, trace_len, iterations) rows of (alpha_k, beta_k, ||dw||_k); returns rows in *rows. */
 pb200_status pb200_get_trace(pb200_solver *s, double *host_3n, int32_t n, int32_t *rows);
 /* Device pointer + pitch (in doubles) of a field of this block, for callers that stay on the GPU.
- * which: 0 w, 1 r, 2 p, 3 Ap, 4 a, 5 b, 6 D. Rows li=0..nx+1, columns lj=0..ny+1 at ptr[li*pitch+lj]. */
+ * which: 0 w, 1 r, 2 p, 4 a, 5 b, 6 D (3 was Ap, which is never stored: invalid). Rows li=0..nx+1, columns lj=0..ny+1 at ptr[li*pitch+lj]. */
 pb200_status pb200_get_field(pb200_solver *s, int32_t which, double **dev_ptr, int64_t *pitch, int32_t *nx, int32_t *ny);
 /* Measurement aid (bench.py's roofline): restarts from the initial state, runs `iters` iterations as plain
  * launches with CUDA events on the solver stream around each kernel, and returns the mean duration in

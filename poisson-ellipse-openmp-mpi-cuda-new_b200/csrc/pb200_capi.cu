@@ -23,6 +23,7 @@ struct OpBlock {
     Ctl *ctl = nullptr;
     double *part = nullptr;
     double *out = nullptr;
+    double *Ap = nullptr; // A p' as K1 computes it (the solver never stores it)
     cudaStream_t stream = nullptr;
     dim3 k1_grid, k2_grid, init_grid;
     int rows_per_seg = 8;
@@ -32,6 +33,7 @@ struct OpBlock {
         if (ctl) cudaFree(ctl);
         if (part) cudaFree(part);
         if (out) cudaFree(out);
+        if (Ap) cudaFree(Ap);
     }
 
     pb200_status init(const pb200_params &p, int nx, int ny, int gi0 = 0, int gj0 = 0) {
@@ -60,11 +62,12 @@ struct OpBlock {
         c.trace_len = 0;
         st = f.allocate(g);
         if (st != PB200_OK) return st;
-        for (double *q : {f.a, f.b, f.D, f.w, f.r, f.z, f.p[0], f.p[1], f.Ap}) CK(cudaMemset(q, 0, f.elems * sizeof(double)));
+        CK(cudaMalloc(&Ap, f.elems * sizeof(double)));
+        for (double *q : {f.a, f.b, f.D, f.w, f.r, f.p[0], f.p[1], Ap}) CK(cudaMemset(q, 0, f.elems * sizeof(double)));
         const int wcols = (ny + K1_OWN - 1) / K1_OWN;
         k1_grid = dim3((wcols + K1_WARPS - 1) / K1_WARPS, (nx + rows_per_seg - 1) / rows_per_seg, 1);
-        k2_grid = dim3((ny / 2 + 1 + K2_THREADS - 1) / K2_THREADS, (nx + K2_ROWS - 1) / K2_ROWS, 1);
-        init_grid = dim3((g.pitch + INIT_THREADS - 1) / INIT_THREADS, std::min(nx + 2, 1024), 1);
+        k2_grid = k1_grid;
+        init_grid = dim3((ny + INIT_THREADS - 1) / INIT_THREADS, std::min(nx, 1024), 1);
         size_t nb = (size_t)k1_grid.x * k1_grid.y;
         nb = std::max(nb, (size_t)init_grid.x * init_grid.y);
         nb = std::max(nb, (size_t)k2_grid.x * k2_grid.y);
@@ -115,28 +118,16 @@ struct OpBlock {
         CK(cudaGetLastError());
         return PB200_OK;
     }
-    pb200_status init_z() { // z = D^-1 r on every stored cell, ctl->zr_old = (z, r)
-        InitArgs a{};
-        a.r = f.r;
-        a.D = f.D;
-        a.z = f.z;
-        a.partials = part;
-        a.ctl = ctl;
-        a.g = f.g;
-        a.c = c;
-        init_kernel<<<init_grid, INIT_THREADS>>>(a);
-        CK(cudaGetLastError());
-        return PB200_OK;
-    }
     pb200_status k1(bool first, const double *p_old, double *p_new) {
         K1Args a{};
-        a.z = f.z;
+        a.r = f.r;
         a.p_old = p_old;
         a.a = f.a;
         a.b = f.b;
+        a.D = f.D;
         a.cls = f.cls;
         a.p_new = p_new;
-        a.Ap = f.Ap;
+        a.Ap = Ap;
         a.partials = part;
         a.ctl = ctl;
         a.g = f.g;
@@ -156,16 +147,18 @@ struct OpBlock {
         K2Args a{};
         a.w = f.w;
         a.r = f.r;
-        a.z = f.z;
         a.p = p;
-        a.Ap = f.Ap;
+        a.a = f.a;
+        a.b = f.b;
         a.D = f.D;
         a.cls = f.cls;
         a.partials = part;
         a.ctl = ctl;
         a.g = f.g;
         a.c = c;
-        k2_kernel<<<k2_grid, K2_THREADS>>>(a);
+        a.rows_per_seg = rows_per_seg;
+        if (safe_div) k2_kernel<true><<<k2_grid, K2_THREADS>>>(a);
+        else k2_kernel<false><<<k2_grid, K2_THREADS>>>(a);
         CK(cudaGetLastError());
         return PB200_OK;
     }
@@ -294,8 +287,8 @@ pb200_status pb200_get_trace(pb200_solver *s, double *host_3n, int32_t n, int32_
 pb200_status pb200_get_field(pb200_solver *s, int32_t which, double **dev_ptr, int64_t *pitch, int32_t *nx, int32_t *ny) {
     if (!s || !dev_ptr) { set_error("null argument"); return PB200_ERR_INVALID; }
     Solver &S = s->impl;
-    double *tab[7] = {S.f.w, S.f.r, S.f.p[S.last_iter & 1], S.f.Ap, S.f.a, S.f.b, S.f.D};
-    if (which < 0 || which > 6) { set_error("bad field id"); return PB200_ERR_INVALID; }
+    double *tab[7] = {S.f.w, S.f.r, S.f.p[S.last_iter & 1], nullptr, S.f.a, S.f.b, S.f.D};
+    if (which < 0 || which > 6 || !tab[which]) { set_error("bad field id (3 = Ap is never stored)"); return PB200_ERR_INVALID; }
     *dev_ptr = tab[which];
     if (pitch) *pitch = S.f.g.pitch;
     if (nx) *nx = S.f.g.nx;
@@ -351,11 +344,11 @@ pb200_status pb200_op_apply_A(const pb200_params *p, const double *pvec, const d
     ob.scan_coefficients(a);
     ob.scan_coefficients(b);
     TRY(ob.diag()); // classifies the caller's coefficients
-    // z = 0, beta = 1: K1 forms p' = 0 + 1*p = p exactly, then Ap = A p'
+    // r = 0, beta = 1: K1 forms p' = 0/D + 1*p = p exactly, then Ap = A p'
     TRY(ob.set_ctl(1.0, 0.0));
     TRY(ob.k1(false, ob.f.p[0], ob.f.p[1]));
     CK(cudaDeviceSynchronize());
-    TRY(ob.get_interior(Ap, ob.f.Ap));
+    TRY(ob.get_interior(Ap, ob.Ap));
     return PB200_OK;
 }
 
@@ -367,10 +360,13 @@ pb200_status pb200_op_apply_Dinv(const pb200_params *p, const double *r, const d
     TRY(ob.put(ob.f.r, r));
     TRY(ob.put(ob.f.a, a));
     TRY(ob.put(ob.f.b, b));
+    ob.scan_coefficients(a);
+    ob.scan_coefficients(b);
     TRY(ob.diag());
-    TRY(ob.init_z()); // the solver's start-up kernel: z = D^-1 r
+    TRY(ob.set_ctl(0.0, 0.0));
+    TRY(ob.k1(true, ob.f.p[0], ob.f.p[1])); // iteration-1 form of K1: p' = D^-1 r
     CK(cudaDeviceSynchronize());
-    TRY(ob.get_interior(z, ob.f.z));
+    TRY(ob.get_interior(z, ob.f.p[1]));
     return PB200_OK;
 }
 
@@ -388,8 +384,6 @@ pb200_status pb200_op_iteration(const pb200_params *p, double *w, double *r, dou
     ob.scan_coefficients(a);
     ob.scan_coefficients(b);
     TRY(ob.diag());
-    TRY(ob.init_z());
-    CK(cudaDeviceSynchronize());
     TRY(ob.set_ctl(beta, zr_old));
     TRY(ob.k1(first != 0, ob.f.p[0], ob.f.p[1]));
     TRY(ob.k2(ob.f.p[1]));
@@ -403,7 +397,7 @@ pb200_status pb200_op_iteration(const pb200_params *p, double *w, double *r, dou
     TRY(ob.get_interior(w, ob.f.w));
     TRY(ob.get_interior(r, ob.f.r));
     TRY(ob.get_interior(pvec, ob.f.p[1]));
-    if (Ap) TRY(ob.get_interior(Ap, ob.f.Ap));
+    if (Ap) TRY(ob.get_interior(Ap, ob.Ap));
     return PB200_OK;
 }
 

@@ -5,8 +5,8 @@
 //   blocking)            -> one grouped ncclSend/ncclRecv between device buffers, on the solver stream;
 //   3 x MPI_Allreduce of one double per iteration (S4:872, 893, 926)
 //                        -> 2 x ncclAllReduce on the device-resident scalars (1 and 2 doubles).
-// What travels is the boundary of z = D^-1 r (after K2), not of p: K1 recomputes p on the ring from
-// z and its own previous ring values, so one exchange per iteration suffices.
+// What travels is the boundary of r (after K2), not of p: K1 recomputes p on the ring from r, the
+// diagonal class and its own previous ring values, so one exchange per iteration suffices.
 //
 // NCCL is loaded with dlopen at first use: single-GPU users need no NCCL at all, and inside a
 // Python process that already imported torch the same libnccl.so.2 is shared.
@@ -70,7 +70,7 @@ NcclApi &nccl() {
         }                                                                                             \
     } while (0)
 
-// column lj of z (rows 1..nx) <-> contiguous buffer
+// column lj of r (rows 1..nx) <-> contiguous buffer
 __global__ void pack_cols_kernel(const double *__restrict__ r, int nx, int pitch, int ny, double *__restrict__ lo,
                                  double *__restrict__ hi) {
     const int li = 1 + blockIdx.x * blockDim.x + threadIdx.x;
@@ -145,23 +145,23 @@ int Solver::halo_kernels_per_iteration() const {
     return (comm && (comm->down >= 0 || comm->up >= 0)) ? 2 : 0;
 }
 
-void Solver::exchange_z_halo() {
+void Solver::exchange_r_halo() {
     const Geom &g = f.g;
     const bool cols = comm->down >= 0 || comm->up >= 0;
     const int tb = 256, nbk = (g.nx + tb - 1) / tb;
-    if (cols) pack_cols_kernel<<<nbk, tb, 0, stream>>>(f.z, g.nx, g.pitch, g.ny, comm->send_lo, comm->send_hi);
+    if (cols) pack_cols_kernel<<<nbk, tb, 0, stream>>>(f.r, g.nx, g.pitch, g.ny, comm->send_lo, comm->send_hi);
     NcclApi &n = nccl();
     ncclResult_t r = n.GroupStart();
     auto acc = [&](ncclResult_t x) { if (x != ncclSuccess && r == ncclSuccess) r = x; };
     const size_t P = g.pitch;
     // i-direction neighbours share whole rows: contiguous, sent in place (interior cells lj = 1..ny)
     if (comm->left >= 0) {
-        acc(n.Send(f.z + 1 * P + 1, g.ny, ncclDouble, comm->left, comm->nc, stream));
-        acc(n.Recv(f.z + 0 * P + 1, g.ny, ncclDouble, comm->left, comm->nc, stream));
+        acc(n.Send(f.r + 1 * P + 1, g.ny, ncclDouble, comm->left, comm->nc, stream));
+        acc(n.Recv(f.r + 0 * P + 1, g.ny, ncclDouble, comm->left, comm->nc, stream));
     }
     if (comm->right >= 0) {
-        acc(n.Send(f.z + (size_t)g.nx * P + 1, g.ny, ncclDouble, comm->right, comm->nc, stream));
-        acc(n.Recv(f.z + (size_t)(g.nx + 1) * P + 1, g.ny, ncclDouble, comm->right, comm->nc, stream));
+        acc(n.Send(f.r + (size_t)g.nx * P + 1, g.ny, ncclDouble, comm->right, comm->nc, stream));
+        acc(n.Recv(f.r + (size_t)(g.nx + 1) * P + 1, g.ny, ncclDouble, comm->right, comm->nc, stream));
     }
     // j-direction neighbours share columns: packed
     if (comm->down >= 0) {
@@ -174,7 +174,7 @@ void Solver::exchange_z_halo() {
     }
     acc(n.GroupEnd());
     if (r != ncclSuccess && comm->async_err == ncclSuccess) comm->async_err = r;
-    if (cols) unpack_cols_kernel<<<nbk, tb, 0, stream>>>(f.z, g.nx, g.pitch, g.ny, comm->recv_lo, comm->recv_hi);
+    if (cols) unpack_cols_kernel<<<nbk, tb, 0, stream>>>(f.r, g.nx, g.pitch, g.ny, comm->recv_lo, comm->recv_hi);
 }
 
 pb200_status Solver::reduce_norms_host(double *) {

@@ -3,10 +3,10 @@
 // Replaces the seven kernels of the reference (stage4-mpi+cuda/poisson_mpi_cuda_f.cu, "S4"):
 //   setup_kernel  <- fictitious_regions_setup_local (host loop, S4:146-192) + zero_kernel (S4:599-609)
 //   init_kernel   <- apply_Dinv_kernel + dot_kernel at start-up (S4:820-843)
-//   k1_kernel     <- update_p_kernel (S4:663-676) / copy_kernel (S4:612-623) + apply_A_kernel (S4:507-536)
-//                    + dot_kernel for (Ap,p) (S4:574-598)
-//   k2_kernel     <- update_w_r_kernel (S4:626-660) + apply_Dinv_kernel (S4:541-562) + dot_kernel for (z,r)
-//                    + the host-side scalar logic of the loop (S4:872-906, 926-932)
+//   k1_kernel     <- apply_Dinv_kernel (S4:541-562) + update_p_kernel (S4:663-676) / copy_kernel (S4:612-623)
+//                    + apply_A_kernel (S4:507-536) + dot_kernel for (Ap,p) (S4:574-598)
+//   k2_kernel     <- apply_A_kernel again (Ap is recomputed, never stored) + update_w_r_kernel (S4:626-660)
+//                    + apply_Dinv_kernel + dot_kernel for (z,r) + the host-side scalar logic (S4:872-906, 926-932)
 //
 // Arithmetic contract: every element-wise expression keeps the reference's expression tree with
 // one rounding per operation (this file is compiled with -fmad=false; the only fused operations
@@ -52,6 +52,7 @@ struct Consts {
 
 constexpr unsigned CLS_GENERAL = 2u;  // a / b class: read the full array
 constexpr unsigned DCLS_GENERAL = 15u; // D class: read the full array
+constexpr unsigned DCLS_RING = 9u;     // cells outside the global interior: D = 1 (their r is 0)
 
 // class byte of one cell: bits 0-1 a class, bits 2-3 b class, bits 4-7 D class
 __device__ __forceinline__ unsigned coef_class(double v, double inv_eps) {
@@ -221,13 +222,13 @@ __global__ void __launch_bounds__(256) setup_kernel(Geom g, Consts c, double *__
     if (lj >= g.pitch) return;
     const size_t o = (size_t)li * g.pitch + lj;
     double va = 0.0, vb = 0.0, vD = 1.0, vr = 0.0;
-    unsigned vc = CLS_GENERAL | (CLS_GENERAL << 2) | (DCLS_GENERAL << 4);
+    unsigned vc = CLS_GENERAL | (CLS_GENERAL << 2) | (DCLS_RING << 4);
     if (lj <= g.ny + 1) {
         const int gi = g.gi0 + li, gj = g.gj0 + lj;
         va = coef_a(c, gi, gj);
         vb = coef_b(c, gi, gj);
         const unsigned ca = coef_class(va, c.inv_eps), cb = coef_class(vb, c.inv_eps);
-        unsigned cD = DCLS_GENERAL;
+        unsigned cD = DCLS_RING;
         if (gi >= 1 && gi <= g.M - 1 && gj >= 1 && gj <= g.N - 1) {
             const double x = c.A1 + gi * c.h1, y = c.A2 + gj * c.h2;
             vr = (x * x + c.ell_c * y * y < 1.0) ? c.f_val : 0.0; // S4:32-34, 189
@@ -257,10 +258,10 @@ __global__ void __launch_bounds__(256) diag_kernel(Geom g, Consts c, const doubl
     if (lj >= g.pitch) return;
     const size_t o = (size_t)li * g.pitch + lj;
     double vD = 1.0;
-    unsigned vc = CLS_GENERAL | (CLS_GENERAL << 2) | (DCLS_GENERAL << 4);
+    unsigned vc = CLS_GENERAL | (CLS_GENERAL << 2) | (DCLS_RING << 4);
     if (lj <= g.ny + 1) {
         const unsigned ca = coef_class(a[o], c.inv_eps), cb = coef_class(b[o], c.inv_eps);
-        unsigned cD = DCLS_GENERAL;
+        unsigned cD = DCLS_RING;
         if (li >= 1 && li <= g.nx && lj >= 1 && lj <= g.ny) {
             const double a_ip = a[o + g.pitch], b_jp = b[o + 1];
             vD = (a_ip + a[o]) / c.h1h1 + (b_jp + b[o]) / c.h2h2;
@@ -302,13 +303,11 @@ __device__ __forceinline__ double precond_div(double r, double D) {
 }
 
 // ------------------------------------------------------------------------------------------
-// init: z = D^-1 r on every stored cell (ring included: the ring's r and D were computed by
-// setup_kernel, so no exchange is needed), zr_old = (z, r) over the interior (S4:820-843).
+// init: zr_old = (D^-1 r, r) over the interior (S4:820-843). z itself is never stored.
 constexpr int INIT_THREADS = 256;
 
 struct InitArgs {
     const double *r, *D;
-    double *z;
     double *partials;
     Ctl *ctl;
     Geom g;
@@ -317,15 +316,13 @@ struct InitArgs {
 
 __global__ void __launch_bounds__(INIT_THREADS) init_kernel(const InitArgs A) {
     const Geom g = A.g;
-    const int lj = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lj = 1 + blockIdx.x * blockDim.x + threadIdx.x;
     double acc[1] = {0.0};
-    if (lj < g.pitch)
-        for (int li = blockIdx.y; li <= g.nx + 1; li += gridDim.y) {
+    if (lj <= g.ny)
+        for (int li = 1 + blockIdx.y; li <= g.nx; li += gridDim.y) {
             const size_t o = (size_t)li * g.pitch + lj;
             const double r = A.r[o];
-            const double z = (lj <= g.ny + 1) ? precond_div(r, A.D[o]) : 0.0;
-            A.z[o] = z;
-            if (li >= 1 && li <= g.nx && lj >= 1 && lj <= g.ny) acc[0] += z * r; // S4:594
+            acc[0] += precond_div(r, A.D[o]) * r; // S4:559, 594
         }
     double tot[1];
     if (grid_reduce<1, INIT_THREADS>(acc, A.partials, &A.ctl->ticket[1], tot)) {
@@ -336,21 +333,26 @@ __global__ void __launch_bounds__(INIT_THREADS) init_kernel(const InitArgs A) {
 }
 
 // ------------------------------------------------------------------------------------------
-// K1: p' = z + beta p ; Ap = A p' ; partial (Ap,p').
+// The two kernels of an iteration. Both march down the grid with the same skeleton:
 //
-// A warp owns 62 adjacent columns and marches down a segment of rows. Lane l holds columns
-// s+2l, s+2l+1 of a 64-column window [s, s+64), s = 62*warp_column: the window's first and last
-// column are the left/right neighbours of the owned range, recomputed instead of exchanged, so
-// warps never synchronise with each other.
+// A warp owns 62 adjacent columns and a segment of rows. Lane l holds columns s+2l, s+2l+1 of a
+// 64-column window [s, s+64), s = 62*warp_column: the window's first and last column are the
+// left/right neighbours of the owned range, recomputed instead of exchanged, so warps never
+// synchronise with each other. p' of the current row and the flux through its lower face live in
+// registers; each step brings in row i+1.
 //
 // The operator is evaluated in flux form, which is the reference's expression tree term by term
 // (S4:526-535): Ax = -1/h1 * (Fx(i+1/2) - Fx(i-1/2)) with Fx(i+1/2) = a(i+1,j)*(p(i+1,j)-p(i,j))/h1.
 // The flux through a face is the same floating-point expression for the two cells that share the
 // face, so it is computed once: Fx(i+1/2) is carried to the next row in a register, Fy(j+1/2) is
-// passed to the neighbouring lane by shuffle. Per row a lane loads 16 bytes each of z and p plus the
-// 2 class bytes of its cells (a and b are decoded from the class; the full arrays are touched only on
-// the cells the ellipse cuts) and stores 16 bytes each of p', Ap; the operands of row i+2 are requested
-// before row i is computed.
+// passed to the neighbouring lane by shuffle.
+//
+//   K1 (k1_kernel): p' = D^-1 r + beta p  (S4:559, 675), stored; Ap = A p' stays in registers and only
+//                   its inner product with p' leaves the kernel (S4:866). 25 B per cell: r, p, class in; p' out.
+//   K2 (k2_kernel): recomputes Ap = A p' from the stored p' (bit-identical: same expressions), then
+//                   w += alpha p', r -= alpha Ap, sum dw^2, z = D^-1 r, sum z r (S4:640-656, 559, 920) and the scalar
+//                   tail of the iteration. 41 B per cell: p', w, r, class in; w, r out.
+// Neither Ap nor z is ever written to memory; a, b, D are decoded from one class byte per cell.
 
 constexpr int K1_WARPS = 8;
 constexpr int K1_THREADS = K1_WARPS * 32;
@@ -358,16 +360,21 @@ constexpr int K1_OWN = 62; // owned columns per warp
 #ifndef PB200_K1_MINB
 #define PB200_K1_MINB 4 // resident CTAs per SM the register allocation is held to (tuned: see DESIGN.md)
 #endif
+#ifndef PB200_K2_MINB
+#define PB200_K2_MINB 3
+#endif
 #ifndef PB200_K1_UNROLL
 #define PB200_K1_UNROLL 1
 #endif
-constexpr int K1_MIN_CTAS = PB200_K1_MINB;
 constexpr int K1_UNROLL = PB200_K1_UNROLL;
+constexpr int K2_THREADS = K1_THREADS;
 
 struct K1Args {
-    const double *z, *p_old, *a, *b; // a, b: full arrays, read only where the class says "general"
+    const double *r, *p_old;
+    const double *a, *b, *D; // full arrays, read only where the class says "general"
     const unsigned char *cls;
-    double *p_new, *Ap;
+    double *p_new;
+    double *Ap; // operator entry points only (null in the solver): store A p'
     double *partials; // [nblocks]
     Ctl *ctl;
     Geom g;
@@ -375,17 +382,25 @@ struct K1Args {
     int rows_per_seg;
 };
 
-struct RowIn {
-    double2 z, q;  // row n = i+1
-    unsigned cls;  // class bytes of the lane's two columns in row n (low byte = first column)
+struct K2Args {
+    double *w, *r;
+    const double *p;
+    const double *a, *b, *D;
+    const unsigned char *cls;
+    double *partials; // [2][nblocks]
+    double *trace;    // [trace_len][3] or null
+    Ctl *ctl;
+    Geom g;
+    Consts c;
+    int rows_per_seg;
 };
-
-__device__ __forceinline__ double class_value(unsigned k, double inv_eps) { return (k & 1u) ? inv_eps : 1.0; }
 
 struct Flux {
     double2 fx;     // Fx(i+1/2) for the lane's two columns
     double fm, fr;  // Fy between the lane's columns, and right of its second column
 };
+
+__device__ __forceinline__ double class_value(unsigned k, double inv_eps) { return (k & 1u) ? inv_eps : 1.0; }
 
 // Fluxes of one row. SAFE: IEEE divides (coefficients or p' outside div_const's proven range).
 template <bool SAFE>
@@ -414,6 +429,15 @@ __device__ __noinline__ Flux row_fluxes_slow(const double2 an, const double2 pn,
     return row_fluxes<true>(an, pn, pc, bc, br, pr, h1, 0.0, h2, 0.0);
 }
 
+// r / D for a diagonal taken from the class table: D and RN(1/D) are known, so the quotient is two exact-residual
+// corrections of r*RN(1/D) (see div_const); IEEE divide when r is outside the proven range.
+__device__ __forceinline__ double lut_div(double r, double2 DR) {
+    double q = div_const_nocheck(r, DR.x, DR.y);
+    if (!in_div_range(r)) q = precond_div(r, DR.x);
+    return q;
+}
+__device__ __noinline__ double precond_div_general(double r, const double *D) { return precond_div(r, __ldg(D)); }
+
 // Branch-free predicated stores of a column pair: the full 16-byte store for lanes whose two columns are
 // both writable, 8-byte stores for the lanes at the edge of the owned range.
 __device__ __forceinline__ void st2_pred(double *ptr, const double2 v, const int both, const int only_x, const int only_y) {
@@ -425,73 +449,123 @@ __device__ __forceinline__ void st2_pred(double *ptr, const double2 v, const int
                  :: "l"(ptr), "d"(v.x), "d"(v.y), "r"(both), "r"(only_x), "r"(only_y) : "memory");
 }
 
+// What a lane knows about its place in the march (computed once per kernel).
+struct Lane {
+    int lane, s, c0, i_lo, i_hi;
+    bool ld_ok, own_x, own_y;
+    int ap_b, ap_x, ap_y; // store predicates for interior outputs (Ap, w, r)
+    int pw_b, pw_x, pw_y; // store predicates for p' (interior + ring)
+};
+
+__device__ __forceinline__ Lane make_lane(const Geom &g, int rows_per_seg) {
+    Lane L;
+    L.lane = threadIdx.x & 31;
+    L.s = (blockIdx.x * K1_WARPS + (threadIdx.x >> 5)) * K1_OWN;
+    L.c0 = L.s + 2 * L.lane;
+    L.i_lo = 1 + blockIdx.y * rows_per_seg;
+    L.i_hi = min(g.nx, L.i_lo + rows_per_seg - 1);
+    L.ld_ok = (L.c0 + 1 < g.pitch);
+    L.own_x = (L.lane > 0) && (L.c0 <= g.ny);
+    L.own_y = (L.lane < 31) && (L.c0 + 1 <= g.ny);
+    const bool wr_x = (L.c0 <= g.ny + 1) && (L.lane > 0 || L.s == 0);
+    const bool wr_y = (L.c0 + 1 <= g.ny + 1) && (L.lane < 31 || L.c0 + 1 == g.ny + 1);
+    L.ap_b = L.own_x && L.own_y;
+    L.ap_x = L.own_x && !L.own_y;
+    L.ap_y = L.own_y && !L.own_x;
+    L.pw_b = wr_x && wr_y;
+    L.pw_x = wr_x && !wr_y;
+    L.pw_y = wr_y && !wr_x;
+    return L;
+}
+
+// Coefficients of one step from the class bytes: a of row i+1 (cls_n), b of row i (cls_c and the next lane's
+// cls_r); cells cut by the ellipse read the exact value from the full arrays.
+__device__ __forceinline__ void decode_ab(const unsigned cls_n, const unsigned cls_c, const unsigned cls_r, const int lane,
+                                          const double inv_eps, const double *a_n, const double *b_c, double2 &an,
+                                          double2 &bc, double &br) {
+    an = make_double2(class_value(cls_n, inv_eps), class_value(cls_n >> 8, inv_eps));
+    bc = make_double2(class_value(cls_c >> 2, inv_eps), class_value(cls_c >> 10, inv_eps));
+    br = class_value(cls_r >> 2, inv_eps);
+    const unsigned general = (cls_n & 0x0202u) | (cls_c & 0x0808u) | ((lane < 31) ? (cls_r & 0x0008u) : 0u);
+    if (__any_sync(0xffffffffu, general != 0u)) {
+        if (cls_n & 0x0002u) an.x = __ldg(a_n);
+        if (cls_n & 0x0200u) an.y = __ldg(a_n + 1);
+        if (cls_c & 0x0008u) bc.x = __ldg(b_c);
+        if (cls_c & 0x0800u) bc.y = __ldg(b_c + 1);
+        if ((lane < 31) && (cls_r & 0x0008u)) br = __ldg(b_c + 2);
+    }
+}
+
+// D^-1 r for the lane's two cells of one row (S4:559), D from the class table (general cells: full array).
+__device__ __forceinline__ double2 precond_pair(const double2 r, const unsigned cls, const double2 *s_lut, const double *D_row) {
+    const unsigned kx = (cls >> 4) & 15u, ky = (cls >> 12) & 15u;
+    double2 z;
+    z.x = lut_div(r.x, s_lut[kx]);
+    z.y = lut_div(r.y, s_lut[ky]);
+    if (__any_sync(0xffffffffu, kx == DCLS_GENERAL || ky == DCLS_GENERAL)) {
+        if (kx == DCLS_GENERAL) z.x = precond_div_general(r.x, D_row);
+        if (ky == DCLS_GENERAL) z.y = precond_div_general(r.y, D_row + 1);
+    }
+    return z;
+}
+
 // FIRST: iteration 1, p' = z (S4:830). SAFE: coefficients not verified to be in div_const's range
-// (operator entry points with caller-supplied a, b): every divide is the IEEE one.
+// (operator entry points with caller-supplied a, b): every stencil divide is the IEEE one.
 template <bool FIRST, bool SAFE>
 __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1Args A) {
     Ctl *ctl = A.ctl;
+    __shared__ double2 s_lut[16];
     if (*reinterpret_cast<volatile int *>(&ctl->done)) return;
+    if (threadIdx.x < 16) s_lut[threadIdx.x] = make_double2(A.c.lutD[threadIdx.x], A.c.lutR[threadIdx.x]);
+    __syncthreads();
     const Geom g = A.g;
     const double h1 = A.c.h1, h2 = A.c.h2, rh1 = A.c.rh1, rh2 = A.c.rh2, mih1 = A.c.mih1, mih2 = A.c.mih2;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int s = (blockIdx.x * K1_WARPS + warp) * K1_OWN;
-    const int c0 = s + 2 * lane;
-    const int i_lo = 1 + blockIdx.y * A.rows_per_seg;
-    const int i_hi = min(g.nx, i_lo + A.rows_per_seg - 1);
+    const double inv_eps = A.c.inv_eps;
+    const Lane L = make_lane(g, A.rows_per_seg);
     const double beta = FIRST ? 0.0 : ctl->beta;
 
     double acc[1] = {0.0};
-    if (s + 1 <= g.ny) { // warp-uniform: this warp owns at least one interior column
-        const bool ld_ok = (c0 + 1 < g.pitch);
-        // stencil outputs: owned columns that are interior cells
-        const bool own_x = (lane > 0) && (c0 <= g.ny);
-        const bool own_y = (lane < 31) && (c0 + 1 <= g.ny);
-        // p' is also kept up to date on the ring (it is the neighbour block's boundary value)
-        const bool wr_x = (c0 <= g.ny + 1) && (lane > 0 || s == 0);
-        const bool wr_y = (c0 + 1 <= g.ny + 1) && (lane < 31 || c0 + 1 == g.ny + 1);
-        const int ap_b = own_x && own_y, ap_x = own_x && !own_y, ap_y = own_y && !own_x;
-        const int pw_b = wr_x && wr_y, pw_x = wr_x && !wr_y, pw_y = wr_y && !wr_x;
-        const double mx = own_x ? 1.0 : 0.0, my = own_y ? 1.0 : 0.0; // dot-product masks (x*1.0 is exact)
+    if (L.s + 1 <= g.ny) { // warp-uniform: this warp owns at least one interior column
         const size_t P = (size_t)g.pitch;
-        const double *zb = A.z + c0, *qb = A.p_old + c0, *ab = A.a + c0, *bb = A.b + c0;
-        const unsigned char *cb = A.cls + c0;
-        double *pob = A.p_new + c0, *apb = A.Ap + c0;
-        const double inv_eps = A.c.inv_eps;
+        const double *rb = A.r + L.c0, *qb = A.p_old + L.c0, *ab = A.a + L.c0, *bb = A.b + L.c0, *Db = A.D + L.c0;
+        const unsigned char *cb = A.cls + L.c0;
+        double *pob = A.p_new + L.c0;
+        double *apb = A.Ap ? A.Ap + L.c0 : nullptr;
 
+        struct RowIn {
+            double2 r, q;  // row n = i+1
+            unsigned cls;  // class bytes of the lane's two columns in row n (low byte = first column)
+        };
         auto load_row = [&](int n) {
             RowIn in;
             const size_t o = (size_t)n * P;
-            in.z = ld2(zb, o, ld_ok);
-            in.q = FIRST ? make_double2(0.0, 0.0) : ld2(qb, o, ld_ok);
-            in.cls = ld_ok ? (unsigned)__ldg(reinterpret_cast<const unsigned short *>(cb + o)) : 0u;
+            in.r = ld2(rb, o, L.ld_ok);
+            in.q = FIRST ? make_double2(0.0, 0.0) : ld2(qb, o, L.ld_ok);
+            in.cls = L.ld_ok ? (unsigned)__ldg(reinterpret_cast<const unsigned short *>(cb + o)) : 0u;
             return in;
         };
-        auto p_update = [&](const RowIn &in) {
-            if (FIRST) return in.z;
-            return make_double2(in.z.x + beta * in.q.x, in.z.y + beta * in.q.y); // S4:675
-        };
-        // a of the lane's two columns in row n, from the class bytes (general cells: the full array)
-        auto decode_a = [&](unsigned cls, int n) {
-            double2 a = make_double2(class_value(cls, inv_eps), class_value(cls >> 8, inv_eps));
-            if (__any_sync(0xffffffffu, (cls & 0x0202u) != 0u)) {
-                if (cls & 0x0002u) a.x = __ldg(ab + (size_t)n * P);
-                if (cls & 0x0200u) a.y = __ldg(ab + (size_t)n * P + 1);
-            }
-            return a;
+        auto p_update = [&](const RowIn &in, int n) {
+            const double2 z = precond_pair(in.r, in.cls, s_lut, Db + (size_t)n * P); // S4:559
+            if (FIRST) return z;                                                     // S4:830
+            return make_double2(z.x + beta * in.q.x, z.y + beta * in.q.y);           // S4:675
         };
 
         // rows i_lo-1 and i_lo: p' of both, and the flux through the face between them
-        RowIn in = load_row(i_lo - 1);
-        const double2 pm = p_update(in);
-        if (i_lo == 1) st2_pred(pob, pm, pw_b, pw_x, pw_y); // ring row 0
-        in = load_row(i_lo);
-        double2 pc = p_update(in);
+        RowIn in = load_row(L.i_lo - 1);
+        const double2 pm = p_update(in, L.i_lo - 1);
+        if (L.i_lo == 1) st2_pred(pob, pm, L.pw_b, L.pw_x, L.pw_y); // ring row 0
+        in = load_row(L.i_lo);
+        double2 pc = p_update(in, L.i_lo);
         unsigned cls_c = in.cls;
-        st2_pred(pob + (size_t)i_lo * P, pc, pw_b, pw_x, pw_y);
+        st2_pred(pob + (size_t)L.i_lo * P, pc, L.pw_b, L.pw_x, L.pw_y);
         bool bad_c = !SAFE && !(in_div_range(pm.x) && in_div_range(pm.y) && in_div_range(pc.x) && in_div_range(pc.y));
         double2 fxl;
         {
-            const double2 ac = decode_a(cls_c, i_lo);
+            double2 ac = make_double2(class_value(cls_c, inv_eps), class_value(cls_c >> 8, inv_eps));
+            if (__any_sync(0xffffffffu, (cls_c & 0x0202u) != 0u)) {
+                if (cls_c & 0x0002u) ac.x = __ldg(ab + (size_t)L.i_lo * P);
+                if (cls_c & 0x0200u) ac.y = __ldg(ab + (size_t)L.i_lo * P + 1);
+            }
             const double x0 = ac.x * (pc.x - pm.x), x1 = ac.y * (pc.y - pm.y);
             if (SAFE || __any_sync(0xffffffffu, bad_c)) {
                 fxl.x = __ddiv_rn(x0, h1);
@@ -504,21 +578,13 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
 
         // one row: consumes the operands of row i+1, leaves p'(i+1), Fx(i+1/2) and the classes of row i+1
         auto row_step = [&](const int i, const RowIn &cur, const int st_b, const int st_x, const int st_y) {
-            const double2 pn = p_update(cur);
+            const double2 pn = p_update(cur, i + 1);
             st2_pred(pob + (size_t)(i + 1) * P, pn, st_b, st_x, st_y);
             const double pr = shfl_dn1(pc.x); // right neighbour of the lane's second column
             const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
-            double2 an = make_double2(class_value(cur.cls, inv_eps), class_value(cur.cls >> 8, inv_eps));
-            double2 bc = make_double2(class_value(cls_c >> 2, inv_eps), class_value(cls_c >> 10, inv_eps));
-            double br = class_value(cls_r >> 2, inv_eps);
-            const unsigned general = (cur.cls & 0x0202u) | (cls_c & 0x0808u) | ((lane < 31) ? (cls_r & 0x0008u) : 0u);
-            if (__any_sync(0xffffffffu, general != 0u)) { // a cell cut by the ellipse: exact values from the full arrays
-                if (cur.cls & 0x0002u) an.x = __ldg(ab + (size_t)(i + 1) * P);
-                if (cur.cls & 0x0200u) an.y = __ldg(ab + (size_t)(i + 1) * P + 1);
-                if (cls_c & 0x0008u) bc.x = __ldg(bb + (size_t)i * P);
-                if (cls_c & 0x0800u) bc.y = __ldg(bb + (size_t)i * P + 1);
-                if ((lane < 31) && (cls_r & 0x0008u)) br = __ldg(bb + (size_t)i * P + 2);
-            }
+            double2 an, bc;
+            double br;
+            decode_ab(cur.cls, cls_c, cls_r, L.lane, inv_eps, ab + (size_t)(i + 1) * P, bb + (size_t)i * P, an, bc, br);
             Flux f;
             if (SAFE) f = row_fluxes<true>(an, pn, pc, bc, br, pr, h1, rh1, h2, rh2);
             else {
@@ -531,9 +597,9 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
             double2 out;
             out.x = mih1 * (f.fx.x - fxl.x) + mih2 * (f.fm - fl);   // S4:526-535
             out.y = mih1 * (f.fx.y - fxl.y) + mih2 * (f.fr - f.fm);
-            st2_pred(apb + (size_t)i * P, out, ap_b, ap_x, ap_y);
-            acc[0] += (out.x * pc.x) * mx; // S4:594 (masked lanes add +0.0)
-            acc[0] += (out.y * pc.y) * my;
+            if (apb) st2_pred(apb + (size_t)i * P, out, L.ap_b, L.ap_x, L.ap_y);
+            acc[0] += L.own_x ? out.x * pc.x : 0.0; // S4:594
+            acc[0] += L.own_y ? out.y * pc.y : 0.0;
             pc = pn;
             fxl = f.fx;
             cls_c = cur.cls;
@@ -541,16 +607,16 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
 
         // The operands of row i+2 are requested before row i is computed. Deeper software prefetch does not
         // pay (measured): a warp has six scoreboard slots, so waiting for the oldest row also waits for newer
-        // ones; latency is hidden by running many warps per SM instead (K1_MIN_CTAS).
-        const int last = (i_hi == g.nx); // row i_hi+1 belongs to the next segment unless it is the ring row nx+1
-        RowIn nxt = load_row(i_lo + 1);
+        // ones; latency is hidden by running many warps per SM instead.
+        const int last = (L.i_hi == g.nx); // row i_hi+1 belongs to the next segment unless it is the ring row nx+1
+        RowIn nxt = load_row(L.i_lo + 1);
 #pragma unroll K1_UNROLL
-        for (int i = i_lo; i < i_hi; ++i) {
+        for (int i = L.i_lo; i < L.i_hi; ++i) {
             const RowIn cur = nxt;
             nxt = load_row(i + 2);
-            row_step(i, cur, pw_b, pw_x, pw_y);
+            row_step(i, cur, L.pw_b, L.pw_x, L.pw_y);
         }
-        row_step(i_hi, nxt, pw_b & last, pw_x & last, pw_y & last);
+        row_step(L.i_hi, nxt, L.pw_b & last, L.pw_x & last, L.pw_y & last);
     }
 
     double tot[1];
@@ -560,24 +626,6 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         if (!A.c.multi) ctl->denom = ctl->red[0];
     }
 }
-
-// ------------------------------------------------------------------------------------------
-// K2: alpha = zr_old/denom ; w += alpha p' ; r -= alpha Ap ; sum dw^2 ; z = D^-1 r ; sum z r ;
-// then (single GPU) the scalar tail of the iteration: stopping test, beta, zr_old.
-
-constexpr int K2_THREADS = 256;
-constexpr int K2_ROWS = 4; // rows per thread
-
-struct K2Args {
-    double *w, *r, *z;
-    const double *p, *Ap, *D; // D: full array, read only where the class says "general"
-    const unsigned char *cls;
-    double *partials; // [2][nblocks]
-    double *trace;    // [trace_len][3] or null
-    Ctl *ctl;
-    Geom g;
-    Consts c;
-};
 
 // The scalar tail of one iteration (S4:893-906, 926-932), run by exactly one thread.
 __device__ __forceinline__ void finalize_iteration(Ctl *ctl, const Consts &c, double *trace, double alpha, double diff2,
@@ -610,14 +658,8 @@ __device__ __forceinline__ void finalize_iteration(Ctl *ctl, const Consts &c, do
     }
 }
 
-// r / D for a diagonal taken from the class table: D and RN(1/D) are known, so the quotient is two exact-residual
-// corrections of r*RN(1/D) (see div_const); IEEE divide when r is outside the proven range.
-__device__ __forceinline__ double lut_div(double r, double2 DR) {
-    const double q = div_const_nocheck(r, DR.x, DR.y);
-    return in_div_range(r) ? q : precond_div(r, DR.x);
-}
-
-__global__ void __launch_bounds__(K2_THREADS) k2_kernel(const K2Args A) {
+template <bool SAFE>
+__global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2Args A) {
     Ctl *ctl = A.ctl;
     __shared__ double2 s_lut[16];
     if (*reinterpret_cast<volatile int *>(&ctl->done)) return;
@@ -636,60 +678,101 @@ __global__ void __launch_bounds__(K2_THREADS) k2_kernel(const K2Args A) {
         return;
     }
     const double alpha = ctl->zr_old / denom; // S4:877
-    const int c0 = 2 * (blockIdx.x * K2_THREADS + threadIdx.x);
-    const int li0 = 1 + blockIdx.y * K2_ROWS;
-    const bool vx = (c0 >= 1) && (c0 <= g.ny);
-    const bool vy = (c0 + 1 <= g.ny);
+    const double h1 = A.c.h1, h2 = A.c.h2, rh1 = A.c.rh1, rh2 = A.c.rh2, mih1 = A.c.mih1, mih2 = A.c.mih2;
+    const double inv_eps = A.c.inv_eps;
+    const Lane L = make_lane(g, A.rows_per_seg);
+
     double acc[2] = {0.0, 0.0};
-    if (vx || vy) {
-        double2 w[K2_ROWS], r[K2_ROWS], p[K2_ROWS], q[K2_ROWS];
-        unsigned cl[K2_ROWS];
-#pragma unroll
-        for (int t = 0; t < K2_ROWS; ++t) {
-            const int li = li0 + t;
-            const bool ok = li <= g.nx;
-            const size_t o = (size_t)li * g.pitch + c0;
-            r[t] = ld2(A.r, o, ok);
-            cl[t] = ok ? (unsigned)__ldg(reinterpret_cast<const unsigned short *>(A.cls + o)) : 0u;
-            w[t] = ld2(A.w, o, ok);
-            p[t] = ld2(A.p, o, ok);
-            q[t] = ld2(A.Ap, o, ok);
-        }
-#pragma unroll
-        for (int t = 0; t < K2_ROWS; ++t) {
-            const int li = li0 + t;
-            if (li > g.nx) break;
-            const size_t o = (size_t)li * g.pitch + c0;
-            double2 wn, rn, zn;
-            wn.x = w[t].x + alpha * p[t].x; // S4:647
-            wn.y = w[t].y + alpha * p[t].y;
-            rn.x = r[t].x - alpha * q[t].x; // S4:648
-            rn.y = r[t].y - alpha * q[t].y;
-            const double dx = wn.x - w[t].x, dy = wn.y - w[t].y; // S4:653
-            const unsigned kx = (cl[t] >> 4) & 15u, ky = (cl[t] >> 12) & 15u;
-            zn.x = lut_div(rn.x, s_lut[kx]); // S4:559
-            zn.y = lut_div(rn.y, s_lut[ky]);
-            if (kx == DCLS_GENERAL) zn.x = precond_div(rn.x, __ldg(A.D + o)); // a cell next to the ellipse boundary
-            if (ky == DCLS_GENERAL) zn.y = precond_div(rn.y, __ldg(A.D + o + 1));
-            if (vx) acc[0] += dx * dx;
-            if (vy) acc[0] += dy * dy;
-            if (vx) acc[1] += zn.x * rn.x; // S4:594
-            if (vy) acc[1] += zn.y * rn.y;
-            if (vx && vy) {
-                *reinterpret_cast<double2 *>(A.w + o) = wn;
-                *reinterpret_cast<double2 *>(A.r + o) = rn;
-                *reinterpret_cast<double2 *>(A.z + o) = zn;
-            } else if (vx) {
-                A.w[o] = wn.x;
-                A.r[o] = rn.x;
-                A.z[o] = zn.x;
+    if (L.s + 1 <= g.ny) {
+        const size_t P = (size_t)g.pitch;
+        const double *pb = A.p + L.c0, *ab = A.a + L.c0, *bb = A.b + L.c0, *Db = A.D + L.c0;
+        const unsigned char *cb = A.cls + L.c0;
+        double *wb = A.w + L.c0, *rb = A.r + L.c0;
+
+        struct RowIn {
+            double2 pn;    // p' of row i+1
+            unsigned cls;  // classes of row i+1
+            double2 w, r;  // row i
+        };
+        auto load_row = [&](int i) {
+            RowIn in;
+            const size_t o = (size_t)i * P;
+            in.pn = ld2(pb, o + P, L.ld_ok);
+            in.cls = L.ld_ok ? (unsigned)__ldg(reinterpret_cast<const unsigned short *>(cb + o + P)) : 0u;
+            in.w = ld2(wb, o, L.ld_ok);
+            in.r = ld2(rb, o, L.ld_ok);
+            return in;
+        };
+
+        // rows i_lo-1 and i_lo of p', the classes of row i_lo, and the flux through the face between them
+        const double2 pm = ld2(pb, (size_t)(L.i_lo - 1) * P, L.ld_ok);
+        double2 pc = ld2(pb, (size_t)L.i_lo * P, L.ld_ok);
+        unsigned cls_c = L.ld_ok ? (unsigned)__ldg(reinterpret_cast<const unsigned short *>(cb + (size_t)L.i_lo * P)) : 0u;
+        bool bad_c = !SAFE && !(in_div_range(pm.x) && in_div_range(pm.y) && in_div_range(pc.x) && in_div_range(pc.y));
+        double2 fxl;
+        {
+            double2 ac = make_double2(class_value(cls_c, inv_eps), class_value(cls_c >> 8, inv_eps));
+            if (__any_sync(0xffffffffu, (cls_c & 0x0202u) != 0u)) {
+                if (cls_c & 0x0002u) ac.x = __ldg(ab + (size_t)L.i_lo * P);
+                if (cls_c & 0x0200u) ac.y = __ldg(ab + (size_t)L.i_lo * P + 1);
+            }
+            const double x0 = ac.x * (pc.x - pm.x), x1 = ac.y * (pc.y - pm.y);
+            if (SAFE || __any_sync(0xffffffffu, bad_c)) {
+                fxl.x = __ddiv_rn(x0, h1);
+                fxl.y = __ddiv_rn(x1, h1);
             } else {
-                A.w[o + 1] = wn.y;
-                A.r[o + 1] = rn.y;
-                A.z[o + 1] = zn.y;
+                fxl.x = div_const_nocheck(x0, h1, rh1);
+                fxl.y = div_const_nocheck(x1, h1, rh1);
             }
         }
+
+        auto row_step = [&](const int i, const RowIn &cur) {
+            const double2 pn = cur.pn;
+            const double pr = shfl_dn1(pc.x);
+            const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
+            double2 an, bc;
+            double br;
+            decode_ab(cur.cls, cls_c, cls_r, L.lane, inv_eps, ab + (size_t)(i + 1) * P, bb + (size_t)i * P, an, bc, br);
+            Flux f;
+            if (SAFE) f = row_fluxes<true>(an, pn, pc, bc, br, pr, h1, rh1, h2, rh2);
+            else {
+                const bool bad_n = !(in_div_range(pn.x) && in_div_range(pn.y));
+                if (__any_sync(0xffffffffu, bad_c | bad_n)) f = row_fluxes_slow(an, pn, pc, bc, br, pr, h1, h2);
+                else f = row_fluxes<false>(an, pn, pc, bc, br, pr, h1, rh1, h2, rh2);
+                bad_c = bad_n;
+            }
+            const double fl = shfl_up1(f.fr);
+            double2 Ap; // S4:526-535: the same expressions K1 evaluated for (Ap,p)
+            Ap.x = mih1 * (f.fx.x - fxl.x) + mih2 * (f.fm - fl);
+            Ap.y = mih1 * (f.fx.y - fxl.y) + mih2 * (f.fr - f.fm);
+            double2 wn, rn;
+            wn.x = cur.w.x + alpha * pc.x; // S4:647
+            wn.y = cur.w.y + alpha * pc.y;
+            rn.x = cur.r.x - alpha * Ap.x; // S4:648
+            rn.y = cur.r.y - alpha * Ap.y;
+            const double dx = wn.x - cur.w.x, dy = wn.y - cur.w.y; // S4:653
+            const double2 zn = precond_pair(rn, cls_c, s_lut, Db + (size_t)i * P); // S4:559
+            acc[0] += L.own_x ? dx * dx : 0.0;
+            acc[0] += L.own_y ? dy * dy : 0.0;
+            acc[1] += L.own_x ? zn.x * rn.x : 0.0; // S4:594
+            acc[1] += L.own_y ? zn.y * rn.y : 0.0;
+            st2_pred(wb + (size_t)i * P, wn, L.ap_b, L.ap_x, L.ap_y);
+            st2_pred(rb + (size_t)i * P, rn, L.ap_b, L.ap_x, L.ap_y);
+            pc = pn;
+            fxl = f.fx;
+            cls_c = cur.cls;
+        };
+
+        RowIn nxt = load_row(L.i_lo);
+#pragma unroll 1
+        for (int i = L.i_lo; i < L.i_hi; ++i) {
+            const RowIn cur = nxt;
+            nxt = load_row(i + 1);
+            row_step(i, cur);
+        }
+        row_step(L.i_hi, nxt);
     }
+
     double tot[2];
     if (grid_reduce<2, K2_THREADS>(acc, A.partials, &ctl->ticket[1], tot)) {
         const double zr = tot[1] * A.c.h1 * A.c.h2; // S3:191

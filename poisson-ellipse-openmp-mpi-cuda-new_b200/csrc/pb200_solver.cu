@@ -114,7 +114,7 @@ bool coef_in_div_range(double v) {
 Fields::~Fields() { release(); }
 
 void Fields::release() {
-    double **all[] = {&a, &b, &D, &w, &r, &z, &p[0], &p[1], &Ap};
+    double **all[] = {&a, &b, &D, &w, &r, &p[0], &p[1]};
     for (double **q : all) {
         if (*q) cudaFree(*q);
         *q = nullptr;
@@ -126,7 +126,7 @@ void Fields::release() {
 pb200_status Fields::allocate(const Geom &geom) {
     g = geom;
     elems = static_cast<size_t>(g.nx + 2) * static_cast<size_t>(g.pitch);
-    double **all[] = {&a, &b, &D, &w, &r, &z, &p[0], &p[1], &Ap};
+    double **all[] = {&a, &b, &D, &w, &r, &p[0], &p[1]};
     for (double **q : all) CK(cudaMalloc(q, elems * sizeof(double)));
     CK(cudaMalloc(&cls, elems));
     return PB200_OK;
@@ -167,12 +167,9 @@ void Solver::plan_launch() {
     rows_per_seg = rows;
     k1_grid.y = (f.g.nx + rows - 1) / rows;
     k1_grid.z = 1;
-    const int cols2 = f.g.ny / 2 + 1; // threads needed: columns 0..ny in pairs
-    k2_grid.x = (cols2 + K2_THREADS - 1) / K2_THREADS;
-    k2_grid.y = (f.g.nx + K2_ROWS - 1) / K2_ROWS;
-    k2_grid.z = 1;
+    k2_grid = k1_grid; // both kernels march over the same decomposition
     norms_grid = dim3((f.g.ny + 255) / 256, std::min(f.g.nx, 512), 1);
-    init_grid = dim3((f.g.pitch + INIT_THREADS - 1) / INIT_THREADS, std::min(f.g.nx + 2, 1024), 1);
+    init_grid = dim3((f.g.ny + INIT_THREADS - 1) / INIT_THREADS, std::min(f.g.nx, 1024), 1);
 }
 
 pb200_status Solver::create(const pb200_params &params) {
@@ -233,10 +230,46 @@ pb200_status Solver::create(const pb200_params &params) {
 
 pb200_status Solver::run_setup() {
     dim3 grid((f.g.pitch + 255) / 256, f.g.nx + 2);
-    setup_kernel<<<grid, 256, 0, stream>>>(f.g, c, f.a, f.b, f.D, f.r, f.w, f.p[0], f.p[1], f.Ap, f.cls);
+    setup_kernel<<<grid, 256, 0, stream>>>(f.g, c, f.a, f.b, f.D, f.r, f.w, f.p[0], f.p[1], nullptr, f.cls);
     ++launches;
     CK(cudaGetLastError());
     return PB200_OK;
+}
+
+K1Args Solver::k1_args(long long k) const {
+    K1Args a{};
+    a.r = f.r;
+    a.p_old = f.p[(k - 1) & 1];
+    a.a = f.a;
+    a.b = f.b;
+    a.D = f.D;
+    a.cls = f.cls;
+    a.p_new = f.p[k & 1];
+    a.Ap = nullptr;
+    a.partials = part1;
+    a.ctl = ctl;
+    a.g = f.g;
+    a.c = c;
+    a.rows_per_seg = rows_per_seg;
+    return a;
+}
+
+K2Args Solver::k2_args(long long k) const {
+    K2Args a{};
+    a.w = f.w;
+    a.r = f.r;
+    a.p = f.p[k & 1];
+    a.a = f.a;
+    a.b = f.b;
+    a.D = f.D;
+    a.cls = f.cls;
+    a.partials = part2;
+    a.trace = trace;
+    a.ctl = ctl;
+    a.g = f.g;
+    a.c = c;
+    a.rows_per_seg = rows_per_seg;
+    return a;
 }
 
 void Solver::launch_k1(const K1Args &a, bool first) {
@@ -249,11 +282,15 @@ void Solver::launch_k1(const K1Args &a, bool first) {
     }
 }
 
+void Solver::launch_k2(const K2Args &a) {
+    if (safe_div) k2_kernel<true><<<k2_grid, K2_THREADS, 0, stream>>>(a);
+    else k2_kernel<false><<<k2_grid, K2_THREADS, 0, stream>>>(a);
+}
+
 void Solver::launch_init() {
     InitArgs ia{};
     ia.r = f.r;
     ia.D = f.D;
-    ia.z = f.z;
     ia.partials = part2;
     ia.ctl = ctl;
     ia.g = f.g;
@@ -262,37 +299,11 @@ void Solver::launch_init() {
 }
 
 void Solver::launch_iteration(long long k, bool first) {
-    K1Args a1{};
-    a1.z = f.z;
-    a1.p_old = f.p[(k - 1) & 1];
-    a1.a = f.a;
-    a1.b = f.b;
-    a1.cls = f.cls;
-    a1.p_new = f.p[k & 1];
-    a1.Ap = f.Ap;
-    a1.partials = part1;
-    a1.ctl = ctl;
-    a1.g = f.g;
-    a1.c = c;
-    a1.rows_per_seg = rows_per_seg;
-    launch_k1(a1, first);
+    launch_k1(k1_args(k), first);
     if (c.multi) allreduce(0, 1);
-    K2Args a2{};
-    a2.w = f.w;
-    a2.r = f.r;
-    a2.z = f.z;
-    a2.p = f.p[k & 1];
-    a2.Ap = f.Ap;
-    a2.D = f.D;
-    a2.cls = f.cls;
-    a2.partials = part2;
-    a2.trace = trace;
-    a2.ctl = ctl;
-    a2.g = f.g;
-    a2.c = c;
-    k2_kernel<<<k2_grid, K2_THREADS, 0, stream>>>(a2);
+    launch_k2(k2_args(k));
     if (c.multi) {
-        exchange_z_halo();
+        exchange_r_halo();
         allreduce(1, 2);
         finalize_kernel<<<1, 1, 0, stream>>>(ctl, c, trace, 0);
     }
@@ -310,7 +321,7 @@ pb200_status Solver::solve(pb200_result *res) {
         pb200_status st = run_setup();
         if (st != PB200_OK) return st;
     }
-    // ---- init (S4:803-843): w = 0 and r = B were written by setup; z = D^-1 r, zr_old = (z, r)
+    // ---- init (S4:803-843): w = 0 and r = B were written by setup; zr_old = (D^-1 r, r)
     CK(cudaMemsetAsync(ctl, 0, sizeof(Ctl), stream));
     CK(cudaMemsetAsync(norms, 0, 4 * sizeof(double), stream));
     launch_init();
@@ -438,16 +449,12 @@ pb200_status Solver::profile_iteration(int iters, double ms_out[2]) {
     std::vector<cudaEvent_t> ev(3 * (size_t)iters);
     for (auto &e : ev) CK(cudaEventCreate(&e));
     for (int k = 1; k <= iters; ++k) {
-        K1Args a1{};
-        a1.z = f.z; a1.p_old = f.p[(k - 1) & 1]; a1.a = f.a; a1.b = f.b; a1.cls = f.cls; a1.p_new = f.p[k & 1]; a1.Ap = f.Ap;
-        a1.partials = part1; a1.ctl = ctl; a1.g = f.g; a1.c = c; a1.rows_per_seg = rows_per_seg;
-        K2Args a2{};
-        a2.w = f.w; a2.r = f.r; a2.z = f.z; a2.p = f.p[k & 1]; a2.Ap = f.Ap; a2.D = f.D; a2.cls = f.cls; a2.partials = part2; a2.ctl = ctl;
-        a2.g = f.g; a2.c = c;
+        K2Args a2 = k2_args(k);
+        a2.trace = nullptr;
         cudaEventRecord(ev[3 * (k - 1) + 0], stream);
-        launch_k1(a1, k == 1);
+        launch_k1(k1_args(k), k == 1);
         cudaEventRecord(ev[3 * (k - 1) + 1], stream);
-        k2_kernel<<<k2_grid, K2_THREADS, 0, stream>>>(a2);
+        launch_k2(a2);
         cudaEventRecord(ev[3 * (k - 1) + 2], stream);
     }
     c = saved;

@@ -24,12 +24,13 @@ Consts make_consts(const pb200_params &p);
 bool coef_in_div_range(double v); // zero, or 2^-400 <= |v| <= 2^400
 int pitch_for(int ny);
 
-// The nine device arrays of one block (the reference's d_a..d_Ap, S4:738-749, plus the stored
-// diagonal D and a second p for the ping-pong; no d_B: r is initialised in place).
+// The device arrays of one block. Hot (touched every iteration): w, r, p[0], p[1] (ping-pong) and one class
+// byte per cell. Cold (written once by setup, read only on cells cut by the ellipse): a, b, D.
+// Of the reference's d_a..d_Ap (S4:738-749), d_B is folded into the initial r, d_z and d_Ap are never stored.
 struct Fields {
     Geom g{};
     size_t elems = 0;
-    double *a = nullptr, *b = nullptr, *D = nullptr, *w = nullptr, *r = nullptr, *z = nullptr, *p[2] = {nullptr, nullptr}, *Ap = nullptr;
+    double *a = nullptr, *b = nullptr, *D = nullptr, *w = nullptr, *r = nullptr, *p[2] = {nullptr, nullptr};
     unsigned char *cls = nullptr; // one class byte per stored cell (pb200_kernels.cuh)
     ~Fields();
     pb200_status allocate(const Geom &geom);
@@ -65,6 +66,9 @@ struct Solver {
     void plan_launch();
     void launch_iteration(long long k, bool first);
     void launch_k1(const K1Args &a, bool first);
+    void launch_k2(const K2Args &a);
+    K1Args k1_args(long long k) const;
+    K2Args k2_args(long long k) const;
     void launch_init();
     int kernels_per_iteration() const;
     pb200_status solve(pb200_result *res);
@@ -77,7 +81,7 @@ struct Solver {
     bool comm_ready() const;
     void destroy_comm();
     void allreduce(int first, int count); // in place on ctl->red[first .. first+count)
-    void exchange_z_halo();               // boundary rows/columns of z -> neighbours' ring
+    void exchange_r_halo();               // boundary rows/columns of r -> neighbours' ring
     int halo_kernels_per_iteration() const;
     pb200_status reduce_norms_host(double h_norms[4]);
 };
