@@ -75,6 +75,7 @@ struct Ctl {
     double red[4];   // [0] denom (this rank) [1] sum dw^2 (this rank, unweighted) [2] (z,r) (this rank) -- all-reduced in place when multi
     long long iter;  // S4:848
     int done;        // loop has ended; later kernels return immediately
+    int fault;       // a value left the range of the unchecked fast divisions: results are void, rerun SAFE
     int status;      // PB200_STOP_*
     int conv_iter;   // first k with diff < delta
     unsigned int ticket[2];
@@ -335,38 +336,41 @@ __global__ void __launch_bounds__(INIT_THREADS) init_kernel(const InitArgs A) {
 // ------------------------------------------------------------------------------------------
 // The two kernels of an iteration. Both march down the grid with the same skeleton:
 //
-// A warp owns 62 adjacent columns and a segment of rows. Lane l holds columns s+2l, s+2l+1 of a
-// 64-column window [s, s+64), s = 62*warp_column: the window's first and last column are the
-// left/right neighbours of the owned range, recomputed instead of exchanged, so warps never
-// synchronise with each other. p' of the current row and the flux through its lower face live in
-// registers; each step brings in row i+1.
+// A warp owns 124 adjacent columns and a segment of rows. Lane l holds the four columns s+4l..s+4l+3 of a
+// 128-column window [s, s+128), s = 124*warp_column (so every lane's 32 bytes are 32-byte aligned and move
+// with one 256-bit load/store). Column s is the left neighbour of the owned range s+1..s+124, column s+125
+// the right neighbour; they are recomputed instead of exchanged, so warps never synchronise with each other.
+// p' of the current row and the flux through its lower face live in registers; each step brings in row i+1.
 //
 // The operator is evaluated in flux form, which is the reference's expression tree term by term
 // (S4:526-535): Ax = -1/h1 * (Fx(i+1/2) - Fx(i-1/2)) with Fx(i+1/2) = a(i+1,j)*(p(i+1,j)-p(i,j))/h1.
 // The flux through a face is the same floating-point expression for the two cells that share the
 // face, so it is computed once: Fx(i+1/2) is carried to the next row in a register, Fy(j+1/2) is
-// passed to the neighbouring lane by shuffle.
+// shared inside the lane and passed to the neighbouring lane by one shuffle.
 //
 //   K1 (k1_kernel): p' = D^-1 r + beta p  (S4:559, 675), stored; Ap = A p' stays in registers and only
 //                   its inner product with p' leaves the kernel (S4:866). 25 B per cell: r, p, class in; p' out.
 //   K2 (k2_kernel): recomputes Ap = A p' from the stored p' (bit-identical: same expressions), then
 //                   w += alpha p', r -= alpha Ap, sum dw^2, z = D^-1 r, sum z r (S4:640-656, 559, 920) and the scalar
 //                   tail of the iteration. 41 B per cell: p', w, r, class in; w, r out.
-// Neither Ap nor z is ever written to memory; a, b, D are decoded from one class byte per cell.
+// Neither Ap nor z is ever written to memory; a, b, D are decoded from one class byte per cell, with
+// warp-uniform fast paths for rows that lie wholly inside or wholly outside the ellipse.
+//
+// Divisions: the fast kernels (SAFE = false) use the exact-residual scheme of div_const without per-call
+// range tests; every p' and every new r is range-tested once (integer pipe) and a hit raises Ctl::fault,
+// upon which the host repeats the solve with the SAFE kernels (IEEE divides everywhere).
 
-constexpr int K1_WARPS = 8;
+constexpr int LW = 4;                  // columns per lane
+constexpr int K1_WIN = 32 * LW;        // window per warp
+constexpr int K1_OWN = K1_WIN - 4;     // owned columns per warp (124: keeps lane offsets 32-byte aligned)
+constexpr int K1_WARPS = 4;
 constexpr int K1_THREADS = K1_WARPS * 32;
-constexpr int K1_OWN = 62; // owned columns per warp
 #ifndef PB200_K1_MINB
 #define PB200_K1_MINB 4 // resident CTAs per SM the register allocation is held to (tuned: see DESIGN.md)
 #endif
 #ifndef PB200_K2_MINB
-#define PB200_K2_MINB 3
+#define PB200_K2_MINB 4
 #endif
-#ifndef PB200_K1_UNROLL
-#define PB200_K1_UNROLL 1
-#endif
-constexpr int K1_UNROLL = PB200_K1_UNROLL;
 constexpr int K2_THREADS = K1_THREADS;
 
 struct K1Args {
@@ -395,127 +399,206 @@ struct K2Args {
     int rows_per_seg;
 };
 
-struct Flux {
-    double2 fx;     // Fx(i+1/2) for the lane's two columns
-    double fm, fr;  // Fy between the lane's columns, and right of its second column
+struct V4 {
+    double v[LW];
 };
+
+__device__ __forceinline__ V4 ldg4_nc(const double *p, bool ok) { // read-only for the whole kernel
+    V4 x;
+    x.v[0] = x.v[1] = x.v[2] = x.v[3] = 0.0;
+    if (ok) asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(x.v[0]), "=d"(x.v[1]), "=d"(x.v[2]), "=d"(x.v[3]) : "l"(p));
+    return x;
+}
+__device__ __forceinline__ V4 ldg4(const double *p, bool ok) { // data this kernel also writes
+    V4 x;
+    x.v[0] = x.v[1] = x.v[2] = x.v[3] = 0.0;
+    if (ok) asm volatile("ld.global.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(x.v[0]), "=d"(x.v[1]), "=d"(x.v[2]), "=d"(x.v[3]) : "l"(p) : "memory");
+    return x;
+}
+// Branch-free predicated store of a lane's four columns: one 256-bit store when all four are writable
+// (mask == 15), else up to four 8-byte stores.
+__device__ __forceinline__ void st4_mask(double *p, const V4 &x, const unsigned mask) {
+    asm volatile("{\n\t.reg .pred pa, p0, p1, p2, p3;\n\t.reg .b32 t;\n\t"
+                 "setp.eq.u32 pa, %5, 15;\n\t"
+                 "and.b32 t, %5, 1;\n\tsetp.ne.and.u32 p0, t, 0, !pa;\n\t"
+                 "and.b32 t, %5, 2;\n\tsetp.ne.and.u32 p1, t, 0, !pa;\n\t"
+                 "and.b32 t, %5, 4;\n\tsetp.ne.and.u32 p2, t, 0, !pa;\n\t"
+                 "and.b32 t, %5, 8;\n\tsetp.ne.and.u32 p3, t, 0, !pa;\n\t"
+                 "@pa st.global.v4.f64 [%0], {%1, %2, %3, %4};\n\t"
+                 "@p0 st.global.f64 [%0], %1;\n\t"
+                 "@p1 st.global.f64 [%0+8], %2;\n\t"
+                 "@p2 st.global.f64 [%0+16], %3;\n\t"
+                 "@p3 st.global.f64 [%0+24], %4;\n\t}"
+                 :: "l"(p), "d"(x.v[0]), "d"(x.v[1]), "d"(x.v[2]), "d"(x.v[3]), "r"(mask) : "memory");
+}
 
 __device__ __forceinline__ double class_value(unsigned k, double inv_eps) { return (k & 1u) ? inv_eps : 1.0; }
 
-// Fluxes of one row. SAFE: IEEE divides (coefficients or p' outside div_const's proven range).
+// 1 when a value is outside the range in which the unchecked exact-residual divisions are proven (see in_div_range)
+__device__ __forceinline__ unsigned range_fault4(const V4 &x) {
+    return (unsigned)!(in_div_range(x.v[0]) && in_div_range(x.v[1]) && in_div_range(x.v[2]) && in_div_range(x.v[3]));
+}
+// the same, looking only at the elements whose mask bit is set
+__device__ __forceinline__ unsigned range_fault4(const V4 &x, const unsigned mask) {
+    unsigned bad = 0u;
+#pragma unroll
+    for (int k = 0; k < LW; ++k) bad |= (unsigned)(((mask >> k) & 1u) && !in_div_range(x.v[k]));
+    return bad;
+}
+
 template <bool SAFE>
-__device__ __forceinline__ Flux row_fluxes(const double2 an, const double2 pn, const double2 pc, const double2 bc,
-                                           const double br, const double pr, const double h1, const double rh1,
-                                           const double h2, const double rh2) {
-    Flux f;
-    const double x0 = an.x * (pn.x - pc.x), x1 = an.y * (pn.y - pc.y); // S4:527
-    const double y0 = bc.y * (pc.y - pc.x), y1 = br * (pr - pc.y);     // S4:531
-    if (SAFE) {
-        f.fx.x = __ddiv_rn(x0, h1);
-        f.fx.y = __ddiv_rn(x1, h1);
-        f.fm = __ddiv_rn(y0, h2);
-        f.fr = __ddiv_rn(y1, h2);
-    } else {
-        f.fx.x = div_const_nocheck(x0, h1, rh1);
-        f.fx.y = div_const_nocheck(x1, h1, rh1);
-        f.fm = div_const_nocheck(y0, h2, rh2);
-        f.fr = div_const_nocheck(y1, h2, rh2);
-    }
-    return f;
-}
-
-__device__ __noinline__ Flux row_fluxes_slow(const double2 an, const double2 pn, const double2 pc, const double2 bc,
-                                             const double br, const double pr, const double h1, const double h2) {
-    return row_fluxes<true>(an, pn, pc, bc, br, pr, h1, 0.0, h2, 0.0);
-}
-
-// r / D for a diagonal taken from the class table: D and RN(1/D) are known, so the quotient is two exact-residual
-// corrections of r*RN(1/D) (see div_const); IEEE divide when r is outside the proven range.
-__device__ __forceinline__ double lut_div(double r, double2 DR) {
-    double q = div_const_nocheck(r, DR.x, DR.y);
-    if (!in_div_range(r)) q = precond_div(r, DR.x);
-    return q;
-}
-__device__ __noinline__ double precond_div_general(double r, const double *D) { return precond_div(r, __ldg(D)); }
-
-// Branch-free predicated stores of a column pair: the full 16-byte store for lanes whose two columns are
-// both writable, 8-byte stores for the lanes at the edge of the owned range.
-__device__ __forceinline__ void st2_pred(double *ptr, const double2 v, const int both, const int only_x, const int only_y) {
-    asm volatile("{\n\t.reg .pred pb, px, py;\n\t"
-                 "setp.ne.s32 pb, %3, 0;\n\tsetp.ne.s32 px, %4, 0;\n\tsetp.ne.s32 py, %5, 0;\n\t"
-                 "@pb st.global.v2.f64 [%0], {%1, %2};\n\t"
-                 "@px st.global.f64 [%0], %1;\n\t"
-                 "@py st.global.f64 [%0+8], %2;\n\t}"
-                 :: "l"(ptr), "d"(v.x), "d"(v.y), "r"(both), "r"(only_x), "r"(only_y) : "memory");
+__device__ __forceinline__ double div_h(double x, double h, double rh) {
+    return SAFE ? __ddiv_rn(x, h) : div_const_nocheck(x, h, rh);
 }
 
 // What a lane knows about its place in the march (computed once per kernel).
 struct Lane {
     int lane, s, c0, i_lo, i_hi;
-    bool ld_ok, own_x, own_y;
-    int ap_b, ap_x, ap_y; // store predicates for interior outputs (Ap, w, r)
-    int pw_b, pw_x, pw_y; // store predicates for p' (interior + ring)
+    bool ld_ok;
+    unsigned own;  // bit k: column c0+k is an interior cell this lane owns (stencil outputs, w, r)
+    unsigned pw;   // bit k: column c0+k gets this lane's p' (owned interior cells + ring columns)
 };
 
 __device__ __forceinline__ Lane make_lane(const Geom &g, int rows_per_seg) {
     Lane L;
     L.lane = threadIdx.x & 31;
     L.s = (blockIdx.x * K1_WARPS + (threadIdx.x >> 5)) * K1_OWN;
-    L.c0 = L.s + 2 * L.lane;
+    L.c0 = L.s + LW * L.lane;
     L.i_lo = 1 + blockIdx.y * rows_per_seg;
     L.i_hi = min(g.nx, L.i_lo + rows_per_seg - 1);
-    L.ld_ok = (L.c0 + 1 < g.pitch);
-    L.own_x = (L.lane > 0) && (L.c0 <= g.ny);
-    L.own_y = (L.lane < 31) && (L.c0 + 1 <= g.ny);
-    const bool wr_x = (L.c0 <= g.ny + 1) && (L.lane > 0 || L.s == 0);
-    const bool wr_y = (L.c0 + 1 <= g.ny + 1) && (L.lane < 31 || L.c0 + 1 == g.ny + 1);
-    L.ap_b = L.own_x && L.own_y;
-    L.ap_x = L.own_x && !L.own_y;
-    L.ap_y = L.own_y && !L.own_x;
-    L.pw_b = wr_x && wr_y;
-    L.pw_x = wr_x && !wr_y;
-    L.pw_y = wr_y && !wr_x;
+    L.ld_ok = (L.c0 + LW - 1 < g.pitch);
+    L.own = 0u;
+    L.pw = 0u;
+#pragma unroll
+    for (int k = 0; k < LW; ++k) {
+        const int col = L.c0 + k;
+        const bool in_own_range = (col >= L.s + 1) && (col <= L.s + K1_OWN);
+        if (in_own_range && col >= 1 && col <= g.ny) L.own |= 1u << k;
+        const bool ring = (L.s == 0 && col == 0) || (col == g.ny + 1 && col == L.s + K1_OWN + 1);
+        if (col <= g.ny + 1 && (in_own_range || ring)) L.pw |= 1u << k;
+    }
     return L;
 }
 
-// Coefficients of one step from the class bytes: a of row i+1 (cls_n), b of row i (cls_c and the next lane's
-// cls_r); cells cut by the ellipse read the exact value from the full arrays.
-__device__ __forceinline__ void decode_ab(const unsigned cls_n, const unsigned cls_c, const unsigned cls_r, const int lane,
-                                          const double inv_eps, const double *a_n, const double *b_c, double2 &an,
-                                          double2 &bc, double &br) {
-    an = make_double2(class_value(cls_n, inv_eps), class_value(cls_n >> 8, inv_eps));
-    bc = make_double2(class_value(cls_c >> 2, inv_eps), class_value(cls_c >> 10, inv_eps));
-    br = class_value(cls_r >> 2, inv_eps);
-    const unsigned general = (cls_n & 0x0202u) | (cls_c & 0x0808u) | ((lane < 31) ? (cls_r & 0x0008u) : 0u);
-    if (__any_sync(0xffffffffu, general != 0u)) {
-        if (cls_n & 0x0002u) an.x = __ldg(a_n);
-        if (cls_n & 0x0200u) an.y = __ldg(a_n + 1);
-        if (cls_c & 0x0008u) bc.x = __ldg(b_c);
-        if (cls_c & 0x0800u) bc.y = __ldg(b_c + 1);
-        if ((lane < 31) && (cls_r & 0x0008u)) br = __ldg(b_c + 2);
+// The numerators of the eight face fluxes of a lane in one row, S4:527/531:
+//   nx[k] = a(i+1, c0+k) * (p(i+1, c0+k) - p(i, c0+k))          (x faces above the lane's cells)
+//   ny[k] = b(i, c0+k+1) * (p(i, c0+k+1) - p(i, c0+k))          (y faces right of the lane's cells)
+// a, b come from the class bytes: cls_n = classes of row i+1, cls_c = row i, cls_r = next lane's row i.
+// Rows that are wholly inside the ellipse (all classes 0: a = b = 1, the product with 1.0 is exact and skipped)
+// or wholly outside (all classes 1: a = b = 1/eps) take warp-uniform shortcuts.
+__device__ __forceinline__ void flux_numerators(const V4 &pn, const V4 &pc, const double pr, const unsigned cls_n,
+                                                const unsigned cls_c, const unsigned cls_r, const int lane,
+                                                const double inv_eps, const double *a_n, const double *b_c, V4 &nx,
+                                                V4 &ny) {
+#pragma unroll
+    for (int k = 0; k < LW; ++k) nx.v[k] = pn.v[k] - pc.v[k];
+#pragma unroll
+    for (int k = 0; k < LW - 1; ++k) ny.v[k] = pc.v[k + 1] - pc.v[k];
+    ny.v[LW - 1] = pr - pc.v[LW - 1];
+    const unsigned ka = cls_n & 0x03030303u, kb = cls_c & 0x0c0c0c0cu;
+    const unsigned kr = ((lane < 31) ? cls_r : cls_c) & 0x0cu; // lane 31 has no right neighbour lane: its last face is unused
+    const bool all0 = (ka | kb | kr) == 0u;
+    const bool all1 = (ka == 0x01010101u) && (kb == 0x04040404u) && (kr == 0x04u);
+    if (__all_sync(0xffffffffu, all0)) return; // a = b = 1
+    if (__all_sync(0xffffffffu, all1)) {
+#pragma unroll
+        for (int k = 0; k < LW; ++k) {
+            nx.v[k] = inv_eps * nx.v[k];
+            ny.v[k] = inv_eps * ny.v[k];
+        }
+        return;
+    }
+    V4 an, bn; // bn[k] = b of the cell right of face k
+#pragma unroll
+    for (int k = 0; k < LW; ++k) an.v[k] = class_value(cls_n >> (8 * k), inv_eps);
+#pragma unroll
+    for (int k = 0; k < LW - 1; ++k) bn.v[k] = class_value(cls_c >> (8 * (k + 1) + 2), inv_eps);
+    bn.v[LW - 1] = class_value(cls_r >> 2, inv_eps);
+    const unsigned general = (cls_n & 0x02020202u) | (cls_c & 0x08080800u) | ((lane < 31) ? (cls_r & 0x08u) : 0u);
+    if (__any_sync(0xffffffffu, general != 0u)) { // a cell cut by the ellipse: exact values from the full arrays
+#pragma unroll
+        for (int k = 0; k < LW; ++k)
+            if (cls_n & (0x02u << (8 * k))) an.v[k] = __ldg(a_n + k);
+#pragma unroll
+        for (int k = 0; k < LW - 1; ++k)
+            if (cls_c & (0x08u << (8 * (k + 1)))) bn.v[k] = __ldg(b_c + k + 1);
+        if ((lane < 31) && (cls_r & 0x08u)) bn.v[LW - 1] = __ldg(b_c + LW);
+    }
+#pragma unroll
+    for (int k = 0; k < LW; ++k) {
+        nx.v[k] = an.v[k] * nx.v[k];
+        ny.v[k] = bn.v[k] * ny.v[k];
     }
 }
 
-// D^-1 r for the lane's two cells of one row (S4:559), D from the class table (general cells: full array).
-__device__ __forceinline__ double2 precond_pair(const double2 r, const unsigned cls, const double2 *s_lut, const double *D_row) {
-    const unsigned kx = (cls >> 4) & 15u, ky = (cls >> 12) & 15u;
-    double2 z;
-    z.x = lut_div(r.x, s_lut[kx]);
-    z.y = lut_div(r.y, s_lut[ky]);
-    if (__any_sync(0xffffffffu, kx == DCLS_GENERAL || ky == DCLS_GENERAL)) {
-        if (kx == DCLS_GENERAL) z.x = precond_div_general(r.x, D_row);
-        if (ky == DCLS_GENERAL) z.y = precond_div_general(r.y, D_row + 1);
+// x-face numerators only (start of a segment: the face between rows i_lo-1 and i_lo)
+__device__ __forceinline__ V4 xface_numerators(const V4 &pc, const V4 &pm, const unsigned cls_c, const double inv_eps,
+                                               const double *a_c) {
+    V4 nx;
+#pragma unroll
+    for (int k = 0; k < LW; ++k) {
+        double a = class_value(cls_c >> (8 * k), inv_eps);
+        if (cls_c & (0x02u << (8 * k))) a = __ldg(a_c + k);
+        nx.v[k] = a * (pc.v[k] - pm.v[k]);
+    }
+    return nx;
+}
+
+// D^-1 r for the lane's four cells of one row (S4:559): D and RN(1/D) from the class table; one broadcast
+// table read when the whole warp sits in one diagonal class, per-cell reads otherwise; cells next to the
+// ellipse boundary (general class) divide by the stored D.
+template <bool SAFE>
+__device__ __forceinline__ V4 precond4(const V4 &r, const unsigned cls, const double2 *s_lut, const double *D_row) {
+    V4 z;
+    const unsigned kd = (cls >> 4) & 0x0f0f0f0fu;
+    const unsigned k0 = __shfl_sync(0xffffffffu, kd, 0) & 0xfu;
+    if (__all_sync(0xffffffffu, kd == k0 * 0x01010101u) && k0 != DCLS_GENERAL) {
+        const double2 DR = s_lut[k0];
+#pragma unroll
+        for (int k = 0; k < LW; ++k) z.v[k] = SAFE ? precond_div(r.v[k], DR.x) : div_const_nocheck(r.v[k], DR.x, DR.y);
+        return z;
+    }
+#pragma unroll
+    for (int k = 0; k < LW; ++k) {
+        const unsigned kk = (kd >> (8 * k)) & 0xfu;
+        const double2 DR = s_lut[kk];
+        z.v[k] = SAFE ? precond_div(r.v[k], DR.x) : div_const_nocheck(r.v[k], DR.x, DR.y);
+        if (kk == DCLS_GENERAL) z.v[k] = precond_div(r.v[k], __ldg(D_row + k));
     }
     return z;
 }
 
-// FIRST: iteration 1, p' = z (S4:830). SAFE: coefficients not verified to be in div_const's range
-// (operator entry points with caller-supplied a, b): every stencil divide is the IEEE one.
+// Stencil of one row for a lane (S4:526-535), given the face numerators. Updates the carried x flux.
+template <bool SAFE>
+__device__ __forceinline__ V4 stencil_row(const V4 &nx, const V4 &ny, V4 &fxl, const double h1, const double rh1,
+                                          const double h2, const double rh2, const double mih1, const double mih2) {
+    V4 fx, fy, out;
+#pragma unroll
+    for (int k = 0; k < LW; ++k) {
+        fx.v[k] = div_h<SAFE>(nx.v[k], h1, rh1);
+        fy.v[k] = div_h<SAFE>(ny.v[k], h2, rh2);
+    }
+    const double fl = shfl_up1(fy.v[LW - 1]); // Fy left of the lane's first column = previous lane's last face
+#pragma unroll
+    for (int k = 0; k < LW; ++k) {
+        const double fym = (k == 0) ? fl : fy.v[k - 1];
+        out.v[k] = mih1 * (fx.v[k] - fxl.v[k]) + mih2 * (fy.v[k] - fym);
+        fxl.v[k] = fx.v[k];
+    }
+    return out;
+}
+
+__device__ __forceinline__ bool stopped(const Ctl *ctl) {
+    return (*reinterpret_cast<const volatile int *>(&ctl->done) | *reinterpret_cast<const volatile int *>(&ctl->fault)) != 0;
+}
+
+// FIRST: iteration 1, p' = z (S4:830). SAFE: IEEE divides everywhere (coefficients or data outside the range in
+// which the exact-residual divisions are proven).
 template <bool FIRST, bool SAFE>
 __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1Args A) {
     Ctl *ctl = A.ctl;
     __shared__ double2 s_lut[16];
-    if (*reinterpret_cast<volatile int *>(&ctl->done)) return;
+    if (stopped(ctl)) return;
     if (threadIdx.x < 16) s_lut[threadIdx.x] = make_double2(A.c.lutD[threadIdx.x], A.c.lutR[threadIdx.x]);
     __syncthreads();
     const Geom g = A.g;
@@ -525,6 +608,7 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
     const double beta = FIRST ? 0.0 : ctl->beta;
 
     double acc[1] = {0.0};
+    unsigned bad = 0u;
     if (L.s + 1 <= g.ny) { // warp-uniform: this warp owns at least one interior column
         const size_t P = (size_t)g.pitch;
         const double *rb = A.r + L.c0, *qb = A.p_old + L.c0, *ab = A.a + L.c0, *bb = A.b + L.c0, *Db = A.D + L.c0;
@@ -533,95 +617,79 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         double *apb = A.Ap ? A.Ap + L.c0 : nullptr;
 
         struct RowIn {
-            double2 r, q;  // row n = i+1
-            unsigned cls;  // class bytes of the lane's two columns in row n (low byte = first column)
+            V4 r, q;       // row n = i+1
+            unsigned cls;  // class bytes of the lane's four columns in row n (byte k = column c0+k)
         };
         auto load_row = [&](int n) {
             RowIn in;
             const size_t o = (size_t)n * P;
-            in.r = ld2(rb, o, L.ld_ok);
-            in.q = FIRST ? make_double2(0.0, 0.0) : ld2(qb, o, L.ld_ok);
-            in.cls = L.ld_ok ? (unsigned)__ldg(reinterpret_cast<const unsigned short *>(cb + o)) : 0u;
+            in.r = ldg4_nc(rb + o, L.ld_ok);
+            if (!FIRST) in.q = ldg4_nc(qb + o, L.ld_ok);
+            in.cls = L.ld_ok ? __ldg(reinterpret_cast<const unsigned *>(cb + o)) : 0u;
             return in;
         };
         auto p_update = [&](const RowIn &in, int n) {
-            const double2 z = precond_pair(in.r, in.cls, s_lut, Db + (size_t)n * P); // S4:559
-            if (FIRST) return z;                                                     // S4:830
-            return make_double2(z.x + beta * in.q.x, z.y + beta * in.q.y);           // S4:675
+            V4 z = precond4<SAFE>(in.r, in.cls, s_lut, Db + (size_t)n * P); // S4:559
+            if (!FIRST) {
+#pragma unroll
+                for (int k = 0; k < LW; ++k) z.v[k] = z.v[k] + beta * in.q.v[k]; // S4:675 (FIRST: p = z, S4:830)
+            }
+            return z;
         };
 
         // rows i_lo-1 and i_lo: p' of both, and the flux through the face between them
         RowIn in = load_row(L.i_lo - 1);
-        const double2 pm = p_update(in, L.i_lo - 1);
-        if (L.i_lo == 1) st2_pred(pob, pm, L.pw_b, L.pw_x, L.pw_y); // ring row 0
+        const V4 pm = p_update(in, L.i_lo - 1);
+        if (L.i_lo == 1) st4_mask(pob, pm, L.pw); // ring row 0
         in = load_row(L.i_lo);
-        double2 pc = p_update(in, L.i_lo);
+        V4 pc = p_update(in, L.i_lo);
         unsigned cls_c = in.cls;
-        st2_pred(pob + (size_t)L.i_lo * P, pc, L.pw_b, L.pw_x, L.pw_y);
-        bool bad_c = !SAFE && !(in_div_range(pm.x) && in_div_range(pm.y) && in_div_range(pc.x) && in_div_range(pc.y));
-        double2 fxl;
+        st4_mask(pob + (size_t)L.i_lo * P, pc, L.pw);
+        if (!SAFE) bad |= range_fault4(pm) | range_fault4(pc);
+        V4 fxl;
         {
-            double2 ac = make_double2(class_value(cls_c, inv_eps), class_value(cls_c >> 8, inv_eps));
-            if (__any_sync(0xffffffffu, (cls_c & 0x0202u) != 0u)) {
-                if (cls_c & 0x0002u) ac.x = __ldg(ab + (size_t)L.i_lo * P);
-                if (cls_c & 0x0200u) ac.y = __ldg(ab + (size_t)L.i_lo * P + 1);
-            }
-            const double x0 = ac.x * (pc.x - pm.x), x1 = ac.y * (pc.y - pm.y);
-            if (SAFE || __any_sync(0xffffffffu, bad_c)) {
-                fxl.x = __ddiv_rn(x0, h1);
-                fxl.y = __ddiv_rn(x1, h1);
-            } else {
-                fxl.x = div_const_nocheck(x0, h1, rh1);
-                fxl.y = div_const_nocheck(x1, h1, rh1);
-            }
+            const V4 nx = xface_numerators(pc, pm, cls_c, inv_eps, ab + (size_t)L.i_lo * P);
+#pragma unroll
+            for (int k = 0; k < LW; ++k) fxl.v[k] = div_h<SAFE>(nx.v[k], h1, rh1);
         }
 
         // one row: consumes the operands of row i+1, leaves p'(i+1), Fx(i+1/2) and the classes of row i+1
-        auto row_step = [&](const int i, const RowIn &cur, const int st_b, const int st_x, const int st_y) {
-            const double2 pn = p_update(cur, i + 1);
-            st2_pred(pob + (size_t)(i + 1) * P, pn, st_b, st_x, st_y);
-            const double pr = shfl_dn1(pc.x); // right neighbour of the lane's second column
+        auto row_step = [&](const int i, const RowIn &cur, const unsigned st_mask) {
+            const V4 pn = p_update(cur, i + 1);
+            st4_mask(pob + (size_t)(i + 1) * P, pn, st_mask);
+            if (!SAFE) bad |= range_fault4(pn);
+            const double pr = shfl_dn1(pc.v[0]); // right neighbour of the lane's last column
             const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
-            double2 an, bc;
-            double br;
-            decode_ab(cur.cls, cls_c, cls_r, L.lane, inv_eps, ab + (size_t)(i + 1) * P, bb + (size_t)i * P, an, bc, br);
-            Flux f;
-            if (SAFE) f = row_fluxes<true>(an, pn, pc, bc, br, pr, h1, rh1, h2, rh2);
-            else {
-                const bool bad_n = !(in_div_range(pn.x) && in_div_range(pn.y));
-                if (__any_sync(0xffffffffu, bad_c | bad_n)) f = row_fluxes_slow(an, pn, pc, bc, br, pr, h1, h2);
-                else f = row_fluxes<false>(an, pn, pc, bc, br, pr, h1, rh1, h2, rh2);
-                bad_c = bad_n;
-            }
-            const double fl = shfl_up1(f.fr); // Fy left of the lane's first column = previous lane's right flux
-            double2 out;
-            out.x = mih1 * (f.fx.x - fxl.x) + mih2 * (f.fm - fl);   // S4:526-535
-            out.y = mih1 * (f.fx.y - fxl.y) + mih2 * (f.fr - f.fm);
-            if (apb) st2_pred(apb + (size_t)i * P, out, L.ap_b, L.ap_x, L.ap_y);
-            acc[0] += L.own_x ? out.x * pc.x : 0.0; // S4:594
-            acc[0] += L.own_y ? out.y * pc.y : 0.0;
+            V4 nx, ny;
+            flux_numerators(pn, pc, pr, cur.cls, cls_c, cls_r, L.lane, inv_eps, ab + (size_t)(i + 1) * P,
+                            bb + (size_t)i * P, nx, ny);
+            const V4 out = stencil_row<SAFE>(nx, ny, fxl, h1, rh1, h2, rh2, mih1, mih2);
+            if (apb) st4_mask(apb + (size_t)i * P, out, L.own);
+#pragma unroll
+            for (int k = 0; k < LW; ++k) acc[0] += ((L.own >> k) & 1u) ? out.v[k] * pc.v[k] : 0.0; // S4:594
             pc = pn;
-            fxl = f.fx;
             cls_c = cur.cls;
         };
 
         // The operands of row i+2 are requested before row i is computed. Deeper software prefetch does not
         // pay (measured): a warp has six scoreboard slots, so waiting for the oldest row also waits for newer
         // ones; latency is hidden by running many warps per SM instead.
-        const int last = (L.i_hi == g.nx); // row i_hi+1 belongs to the next segment unless it is the ring row nx+1
+        const unsigned last = (L.i_hi == g.nx) ? L.pw : 0u; // row i_hi+1 belongs to the next segment unless it is ring row nx+1
         RowIn nxt = load_row(L.i_lo + 1);
-#pragma unroll K1_UNROLL
+#pragma unroll 1
         for (int i = L.i_lo; i < L.i_hi; ++i) {
             const RowIn cur = nxt;
             nxt = load_row(i + 2);
-            row_step(i, cur, L.pw_b, L.pw_x, L.pw_y);
+            row_step(i, cur, L.pw);
         }
-        row_step(L.i_hi, nxt, L.pw_b & last, L.pw_x & last, L.pw_y & last);
+        row_step(L.i_hi, nxt, last);
     }
+    if (bad) ctl->fault = 1;
 
     double tot[1];
     if (grid_reduce<1, K1_THREADS>(acc, A.partials, &ctl->ticket[0], tot)) {
         ctl->red[0] = tot[0] * h1 * h2; // S3:191: sum * h1 * h2
+        ctl->red[3] = (double)*reinterpret_cast<volatile int *>(&ctl->fault);
         ctl->iter = ctl->iter + 1;      // S4:847-848: k
         if (!A.c.multi) ctl->denom = ctl->red[0];
     }
@@ -662,7 +730,7 @@ template <bool SAFE>
 __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2Args A) {
     Ctl *ctl = A.ctl;
     __shared__ double2 s_lut[16];
-    if (*reinterpret_cast<volatile int *>(&ctl->done)) return;
+    if (stopped(ctl)) return;
     if (threadIdx.x < 16) s_lut[threadIdx.x] = make_double2(A.c.lutD[threadIdx.x], A.c.lutR[threadIdx.x]);
     __syncthreads();
     const Geom g = A.g;
@@ -683,6 +751,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
     const Lane L = make_lane(g, A.rows_per_seg);
 
     double acc[2] = {0.0, 0.0};
+    unsigned bad = 0u;
     if (L.s + 1 <= g.ny) {
         const size_t P = (size_t)g.pitch;
         const double *pb = A.p + L.c0, *ab = A.a + L.c0, *bb = A.b + L.c0, *Db = A.D + L.c0;
@@ -690,76 +759,56 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         double *wb = A.w + L.c0, *rb = A.r + L.c0;
 
         struct RowIn {
-            double2 pn;    // p' of row i+1
+            V4 pn;         // p' of row i+1
             unsigned cls;  // classes of row i+1
-            double2 w, r;  // row i
+            V4 w, r;       // row i
         };
         auto load_row = [&](int i) {
             RowIn in;
             const size_t o = (size_t)i * P;
-            in.pn = ld2(pb, o + P, L.ld_ok);
-            in.cls = L.ld_ok ? (unsigned)__ldg(reinterpret_cast<const unsigned short *>(cb + o + P)) : 0u;
-            in.w = ld2(wb, o, L.ld_ok);
-            in.r = ld2(rb, o, L.ld_ok);
+            in.pn = ldg4_nc(pb + o + P, L.ld_ok);
+            in.cls = L.ld_ok ? __ldg(reinterpret_cast<const unsigned *>(cb + o + P)) : 0u;
+            in.w = ldg4(wb + o, L.ld_ok);
+            in.r = ldg4(rb + o, L.ld_ok);
             return in;
         };
 
         // rows i_lo-1 and i_lo of p', the classes of row i_lo, and the flux through the face between them
-        const double2 pm = ld2(pb, (size_t)(L.i_lo - 1) * P, L.ld_ok);
-        double2 pc = ld2(pb, (size_t)L.i_lo * P, L.ld_ok);
-        unsigned cls_c = L.ld_ok ? (unsigned)__ldg(reinterpret_cast<const unsigned short *>(cb + (size_t)L.i_lo * P)) : 0u;
-        bool bad_c = !SAFE && !(in_div_range(pm.x) && in_div_range(pm.y) && in_div_range(pc.x) && in_div_range(pc.y));
-        double2 fxl;
+        const V4 pm = ldg4_nc(pb + (size_t)(L.i_lo - 1) * P, L.ld_ok);
+        V4 pc = ldg4_nc(pb + (size_t)L.i_lo * P, L.ld_ok);
+        unsigned cls_c = L.ld_ok ? __ldg(reinterpret_cast<const unsigned *>(cb + (size_t)L.i_lo * P)) : 0u;
+        V4 fxl;
         {
-            double2 ac = make_double2(class_value(cls_c, inv_eps), class_value(cls_c >> 8, inv_eps));
-            if (__any_sync(0xffffffffu, (cls_c & 0x0202u) != 0u)) {
-                if (cls_c & 0x0002u) ac.x = __ldg(ab + (size_t)L.i_lo * P);
-                if (cls_c & 0x0200u) ac.y = __ldg(ab + (size_t)L.i_lo * P + 1);
-            }
-            const double x0 = ac.x * (pc.x - pm.x), x1 = ac.y * (pc.y - pm.y);
-            if (SAFE || __any_sync(0xffffffffu, bad_c)) {
-                fxl.x = __ddiv_rn(x0, h1);
-                fxl.y = __ddiv_rn(x1, h1);
-            } else {
-                fxl.x = div_const_nocheck(x0, h1, rh1);
-                fxl.y = div_const_nocheck(x1, h1, rh1);
-            }
+            const V4 nx = xface_numerators(pc, pm, cls_c, inv_eps, ab + (size_t)L.i_lo * P);
+#pragma unroll
+            for (int k = 0; k < LW; ++k) fxl.v[k] = div_h<SAFE>(nx.v[k], h1, rh1);
         }
 
         auto row_step = [&](const int i, const RowIn &cur) {
-            const double2 pn = cur.pn;
-            const double pr = shfl_dn1(pc.x);
+            const double pr = shfl_dn1(pc.v[0]);
             const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
-            double2 an, bc;
-            double br;
-            decode_ab(cur.cls, cls_c, cls_r, L.lane, inv_eps, ab + (size_t)(i + 1) * P, bb + (size_t)i * P, an, bc, br);
-            Flux f;
-            if (SAFE) f = row_fluxes<true>(an, pn, pc, bc, br, pr, h1, rh1, h2, rh2);
-            else {
-                const bool bad_n = !(in_div_range(pn.x) && in_div_range(pn.y));
-                if (__any_sync(0xffffffffu, bad_c | bad_n)) f = row_fluxes_slow(an, pn, pc, bc, br, pr, h1, h2);
-                else f = row_fluxes<false>(an, pn, pc, bc, br, pr, h1, rh1, h2, rh2);
-                bad_c = bad_n;
+            V4 nx, ny;
+            flux_numerators(cur.pn, pc, pr, cur.cls, cls_c, cls_r, L.lane, inv_eps, ab + (size_t)(i + 1) * P,
+                            bb + (size_t)i * P, nx, ny);
+            const V4 Ap = stencil_row<SAFE>(nx, ny, fxl, h1, rh1, h2, rh2, mih1, mih2); // the expressions K1 used for (Ap,p)
+            V4 wn, rn;
+#pragma unroll
+            for (int k = 0; k < LW; ++k) {
+                wn.v[k] = cur.w.v[k] + alpha * pc.v[k]; // S4:647
+                rn.v[k] = cur.r.v[k] - alpha * Ap.v[k]; // S4:648
             }
-            const double fl = shfl_up1(f.fr);
-            double2 Ap; // S4:526-535: the same expressions K1 evaluated for (Ap,p)
-            Ap.x = mih1 * (f.fx.x - fxl.x) + mih2 * (f.fm - fl);
-            Ap.y = mih1 * (f.fx.y - fxl.y) + mih2 * (f.fr - f.fm);
-            double2 wn, rn;
-            wn.x = cur.w.x + alpha * pc.x; // S4:647
-            wn.y = cur.w.y + alpha * pc.y;
-            rn.x = cur.r.x - alpha * Ap.x; // S4:648
-            rn.y = cur.r.y - alpha * Ap.y;
-            const double dx = wn.x - cur.w.x, dy = wn.y - cur.w.y; // S4:653
-            const double2 zn = precond_pair(rn, cls_c, s_lut, Db + (size_t)i * P); // S4:559
-            acc[0] += L.own_x ? dx * dx : 0.0;
-            acc[0] += L.own_y ? dy * dy : 0.0;
-            acc[1] += L.own_x ? zn.x * rn.x : 0.0; // S4:594
-            acc[1] += L.own_y ? zn.y * rn.y : 0.0;
-            st2_pred(wb + (size_t)i * P, wn, L.ap_b, L.ap_x, L.ap_y);
-            st2_pred(rb + (size_t)i * P, rn, L.ap_b, L.ap_x, L.ap_y);
-            pc = pn;
-            fxl = f.fx;
+            if (!SAFE) bad |= range_fault4(rn, L.own);
+            const V4 zn = precond4<SAFE>(rn, cls_c, s_lut, Db + (size_t)i * P); // S4:559
+#pragma unroll
+            for (int k = 0; k < LW; ++k) {
+                const bool own = (L.own >> k) & 1u;
+                const double d = wn.v[k] - cur.w.v[k]; // S4:653
+                acc[0] += own ? d * d : 0.0;
+                acc[1] += own ? zn.v[k] * rn.v[k] : 0.0; // S4:594
+            }
+            st4_mask(wb + (size_t)i * P, wn, L.own);
+            st4_mask(rb + (size_t)i * P, rn, L.own);
+            pc = cur.pn;
             cls_c = cur.cls;
         };
 
@@ -772,21 +821,27 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         }
         row_step(L.i_hi, nxt);
     }
+    if (bad) ctl->fault = 1;
 
     double tot[2];
     if (grid_reduce<2, K2_THREADS>(acc, A.partials, &ctl->ticket[1], tot)) {
         const double zr = tot[1] * A.c.h1 * A.c.h2; // S3:191
         ctl->red[1] = tot[0];
         ctl->red[2] = zr;
-        if (!A.c.multi) finalize_iteration(ctl, A.c, A.trace, alpha, tot[0], zr);
+        ctl->red[3] = (double)*reinterpret_cast<volatile int *>(&ctl->fault);
+        if (!A.c.multi && ctl->red[3] == 0.0) finalize_iteration(ctl, A.c, A.trace, alpha, tot[0], zr);
     }
 }
 
-// Multi-GPU: after the all-reduce of red[1..2] (or red[2] at init) every rank runs the same scalar tail.
+// Multi-GPU: after the all-reduce of red[1..3] (or red[2] at init) every rank runs the same scalar tail.
 __global__ void finalize_kernel(Ctl *ctl, Consts c, double *trace, int init) {
-    if (*reinterpret_cast<volatile int *>(&ctl->done)) return;
+    if (stopped(ctl)) return;
     if (init) {
         ctl->zr_old = ctl->red[2];
+        return;
+    }
+    if (ctl->red[3] != 0.0) { // some rank left the range of the fast divisions: every rank stops, the host restarts SAFE
+        ctl->fault = 1;
         return;
     }
     const double denom = ctl->red[0];

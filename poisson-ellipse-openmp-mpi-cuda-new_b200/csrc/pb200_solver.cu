@@ -200,7 +200,7 @@ pb200_status Solver::create(const pb200_params &params) {
     g.N = prm.N;
     c = make_consts(prm);
     // the coefficients are 1, 1/eps or a blend of the two (S4:167-177): div_const's fast path needs them in range
-    safe_div = !(coef_in_div_range(1.0 / c.eps) && coef_in_div_range(c.eps));
+    safe_div = !(coef_in_div_range(1.0 / c.eps) && coef_in_div_range(c.eps) && coef_in_div_range(c.f_val));
     CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     st = f.allocate(g);
     if (st != PB200_OK) return st;
@@ -304,7 +304,7 @@ void Solver::launch_iteration(long long k, bool first) {
     launch_k2(k2_args(k));
     if (c.multi) {
         exchange_r_halo();
-        allreduce(1, 2);
+        allreduce(1, 3);
         finalize_kernel<<<1, 1, 0, stream>>>(ctl, c, trace, 0);
     }
 }
@@ -380,7 +380,7 @@ pb200_status Solver::solve(pb200_result *res) {
             CK(cudaEventRecord(ev_poll[slot], stream));
             if (pending >= 0) { // look at the batch BEFORE the one just queued: the GPU never idles
                 CK(cudaEventSynchronize(ev_poll[pending]));
-                done = h_ctl[pending].done != 0;
+                done = h_ctl[pending].done != 0 || h_ctl[pending].fault != 0;
             }
             pending = slot;
             slot ^= 1;
@@ -408,6 +408,16 @@ pb200_status Solver::solve(pb200_result *res) {
     CK(cudaEventElapsedTime(&ms_call, ev_call0, ev_call1));
     const Ctl &hc = h_ctl[0];
     solved = true;
+    if (hc.fault && !safe_div) {
+        // A value left the range in which the fast divisions are proven exact (|x| outside 2^-400..2^400): the
+        // run is void. Repeat it with IEEE divides everywhere; this handle stays in that mode.
+        safe_div = true;
+        if (graph_exec) {
+            cudaGraphExecDestroy(graph_exec);
+            graph_exec = nullptr;
+        }
+        return solve(res);
+    }
     last_iter = hc.iter;
     if (res) {
         std::memset(res, 0, sizeof(*res));
