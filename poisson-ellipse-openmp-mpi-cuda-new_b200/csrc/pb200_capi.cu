@@ -51,10 +51,13 @@ struct OpBlock {
         g.nx = nx;
         g.ny = ny;
         g.pitch = pitch_for(ny);
+        g.cpitch = cpitch_for(ny);
         g.gi0 = gi0;
         g.gj0 = gj0;
         g.M = p.M;
         g.N = p.N;
+        st = enable_kernel_smem();
+        if (st != PB200_OK) return st;
         c = make_consts(p);
         c.multi = 0;
         c.fixed = 1;
@@ -141,11 +144,11 @@ struct OpBlock {
         a.c = c;
         a.rows_per_seg = rows_per_seg;
         if (first) {
-            if (safe_div) k1_kernel<true, true><<<k1_grid, K1_THREADS>>>(a);
-            else k1_kernel<true, false><<<k1_grid, K1_THREADS>>>(a);
+            if (safe_div) k1_kernel<true, true><<<k1_grid, K1_THREADS, K1_SMEM>>>(a);
+            else k1_kernel<true, false><<<k1_grid, K1_THREADS, K1_SMEM>>>(a);
         } else {
-            if (safe_div) k1_kernel<false, true><<<k1_grid, K1_THREADS>>>(a);
-            else k1_kernel<false, false><<<k1_grid, K1_THREADS>>>(a);
+            if (safe_div) k1_kernel<false, true><<<k1_grid, K1_THREADS, K1_SMEM>>>(a);
+            else k1_kernel<false, false><<<k1_grid, K1_THREADS, K1_SMEM>>>(a);
         }
         CK(cudaGetLastError());
         return PB200_OK;
@@ -164,8 +167,8 @@ struct OpBlock {
         a.g = f.g;
         a.c = c;
         a.rows_per_seg = rows_per_seg;
-        if (safe_div) k2_kernel<true><<<k2_grid, K2_THREADS>>>(a);
-        else k2_kernel<false><<<k2_grid, K2_THREADS>>>(a);
+        if (safe_div) k2_kernel<true><<<k2_grid, K2_THREADS, K2_SMEM>>>(a);
+        else k2_kernel<false><<<k2_grid, K2_THREADS, K2_SMEM>>>(a);
         CK(cudaGetLastError());
         return PB200_OK;
     }

@@ -26,7 +26,22 @@ struct Geom {
     int pitch;    // doubles per row, multiple of 16
     int gi0, gj0; // global index of local (0,0): i_start-1, j_start-1 (S4:156-157)
     int M, N;
+    int cpitch;   // bytes per row of the class map (one 128-byte record per 124-column warp window)
 };
+
+// The class map is stored per warp window so that a warp's 128 class bytes of a row are one aligned
+// 128-byte record (bulk-copyable): byte k of record w of row li belongs to column 124*w + k.
+constexpr int CLS_OWN = 124, CLS_WIN = 128;
+__host__ __device__ __forceinline__ size_t cls_index(int cpitch, int li, int w, int k) {
+    return (size_t)li * (size_t)cpitch + (size_t)w * CLS_WIN + (size_t)k;
+}
+// store the class byte of column lj of row li into every record that covers it (the first 4 columns of a
+// window are also the last 4 of the previous one)
+__device__ __forceinline__ void cls_store(unsigned char *cls, int cpitch, int li, int lj, unsigned v) {
+    const int w = lj / CLS_OWN, k = lj - w * CLS_OWN;
+    if ((w + 1) * CLS_WIN <= cpitch) cls[cls_index(cpitch, li, w, k)] = (unsigned char)v;
+    if (w > 0 && k < CLS_WIN - CLS_OWN) cls[cls_index(cpitch, li, w - 1, k + CLS_OWN)] = (unsigned char)v;
+}
 
 struct Consts {
     double A1, A2;             // rectangle origin (S4:11-12)
@@ -239,7 +254,7 @@ __global__ void __launch_bounds__(256) setup_kernel(Geom g, Consts c, double *__
         }
         vc = ca | (cb << 2) | (cD << 4);
     }
-    if (cls) cls[o] = (unsigned char)vc;
+    if (cls && lj <= g.ny + 1) cls_store(cls, g.cpitch, li, lj, vc);
     a[o] = va;
     b[o] = vb;
     D[o] = vD;
@@ -271,7 +286,7 @@ __global__ void __launch_bounds__(256) diag_kernel(Geom g, Consts c, const doubl
         vc = ca | (cb << 2) | (cD << 4);
     }
     D[o] = vD;
-    cls[o] = (unsigned char)vc;
+    if (lj <= g.ny + 1) cls_store(cls, g.cpitch, li, lj, vc);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -363,7 +378,11 @@ __global__ void __launch_bounds__(INIT_THREADS) init_kernel(const InitArgs A) {
 constexpr int LW = 4;                  // columns per lane
 constexpr int K1_WIN = 32 * LW;        // window per warp
 constexpr int K1_OWN = K1_WIN - 4;     // owned columns per warp (124: keeps lane offsets 32-byte aligned)
-constexpr int K1_WARPS = 4;
+static_assert(K1_OWN == CLS_OWN && K1_WIN == CLS_WIN, "class map records follow the warp windows");
+#ifndef PB200_K1_WARPS
+#define PB200_K1_WARPS 4
+#endif
+constexpr int K1_WARPS = PB200_K1_WARPS;
 constexpr int K1_THREADS = K1_WARPS * 32;
 #ifndef PB200_K1_MINB
 #define PB200_K1_MINB 4 // resident CTAs per SM the register allocation is held to (tuned: see DESIGN.md)
@@ -371,7 +390,19 @@ constexpr int K1_THREADS = K1_WARPS * 32;
 #ifndef PB200_K2_MINB
 #define PB200_K2_MINB 4
 #endif
+#ifndef PB200_STAGES
+#define PB200_STAGES 4
+#endif
 constexpr int K2_THREADS = K1_THREADS;
+// Operand rows reach the SM through the bulk-copy engine (cp.async.bulk -> shared memory, completion on an
+// mbarrier), STAGES rows ahead of the row being computed, one private ring per warp: the bytes in flight no
+// longer depend on registers, scoreboard slots or occupancy.
+constexpr int STAGES = PB200_STAGES;
+constexpr int ROW_BYTES = K1_WIN * 8;                      // one warp window of one row of doubles
+constexpr int K1_STAGE_BYTES = 2 * ROW_BYTES + CLS_WIN;     // r, p, classes of row n
+constexpr int K2_STAGE_BYTES = 3 * ROW_BYTES + CLS_WIN;     // p'(i+1), w(i), r(i), classes of row i+1
+constexpr int K1_SMEM = K1_WARPS * STAGES * K1_STAGE_BYTES;
+constexpr int K2_SMEM = K1_WARPS * STAGES * K2_STAGE_BYTES;
 
 struct K1Args {
     const double *r, *p_old;
@@ -402,6 +433,34 @@ struct K2Args {
 struct V4 {
     double v[LW];
 };
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_LOOP:\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                 "@p bra WAIT_DONE;\n\tbra WAIT_LOOP;\n\tWAIT_DONE:\n\t}" ::"r"(bar),
+                 "r"(parity)
+                 : "memory");
+}
+// a lane's four doubles of a staged row (two 16-byte shared-memory reads)
+__device__ __forceinline__ V4 lds4(const unsigned char *row, int lane) {
+    const double2 *q = reinterpret_cast<const double2 *>(row + 32 * lane);
+    const double2 lo = q[0], hi = q[1];
+    V4 x;
+    x.v[0] = lo.x; x.v[1] = lo.y; x.v[2] = hi.x; x.v[3] = hi.y;
+    return x;
+}
 
 __device__ __forceinline__ V4 ldg4_nc(const double *p, bool ok) { // read-only for the whole kernel
     V4 x;
@@ -453,7 +512,7 @@ __device__ __forceinline__ double div_h(double x, double h, double rh) {
 
 // What a lane knows about its place in the march (computed once per kernel).
 struct Lane {
-    int lane, s, c0, i_lo, i_hi;
+    int lane, warp, wcol, s, c0, i_lo, i_hi;
     bool ld_ok;
     unsigned own;  // bit k: column c0+k is an interior cell this lane owns (stencil outputs, w, r)
     unsigned pw;   // bit k: column c0+k gets this lane's p' (owned interior cells + ring columns)
@@ -462,7 +521,9 @@ struct Lane {
 __device__ __forceinline__ Lane make_lane(const Geom &g, int rows_per_seg) {
     Lane L;
     L.lane = threadIdx.x & 31;
-    L.s = (blockIdx.x * K1_WARPS + (threadIdx.x >> 5)) * K1_OWN;
+    L.warp = threadIdx.x >> 5;
+    L.wcol = blockIdx.x * K1_WARPS + L.warp;
+    L.s = L.wcol * K1_OWN;
     L.c0 = L.s + LW * L.lane;
     L.i_lo = 1 + blockIdx.y * rows_per_seg;
     L.i_hi = min(g.nx, L.i_lo + rows_per_seg - 1);
@@ -597,37 +658,67 @@ __device__ __forceinline__ bool stopped(const Ctl *ctl) {
 template <bool FIRST, bool SAFE>
 __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1Args A) {
     Ctl *ctl = A.ctl;
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ __align__(8) unsigned long long s_bar[K1_WARPS][STAGES];
     __shared__ double2 s_lut[16];
     if (stopped(ctl)) return;
-    if (threadIdx.x < 16) s_lut[threadIdx.x] = make_double2(A.c.lutD[threadIdx.x], A.c.lutR[threadIdx.x]);
-    __syncthreads();
     const Geom g = A.g;
+    const Lane L = make_lane(g, A.rows_per_seg);
+    if (threadIdx.x < 16) s_lut[threadIdx.x] = make_double2(A.c.lutD[threadIdx.x], A.c.lutR[threadIdx.x]);
+    if (L.lane == 0) {
+#pragma unroll
+        for (int st = 0; st < STAGES; ++st) mbar_init(smem_u32(&s_bar[L.warp][st]), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
     const double h1 = A.c.h1, h2 = A.c.h2, rh1 = A.c.rh1, rh2 = A.c.rh2, mih1 = A.c.mih1, mih2 = A.c.mih2;
     const double inv_eps = A.c.inv_eps;
-    const Lane L = make_lane(g, A.rows_per_seg);
     const double beta = FIRST ? 0.0 : ctl->beta;
 
     double acc[1] = {0.0};
     unsigned bad = 0u;
     if (L.s + 1 <= g.ny) { // warp-uniform: this warp owns at least one interior column
         const size_t P = (size_t)g.pitch;
-        const double *rb = A.r + L.c0, *qb = A.p_old + L.c0, *ab = A.a + L.c0, *bb = A.b + L.c0, *Db = A.D + L.c0;
-        const unsigned char *cb = A.cls + L.c0;
+        const double *ab = A.a + L.c0, *bb = A.b + L.c0, *Db = A.D + L.c0;
         double *pob = A.p_new + L.c0;
         double *apb = A.Ap ? A.Ap + L.c0 : nullptr;
 
         struct RowIn {
-            V4 r, q;       // row n = i+1
+            V4 r, q;       // row n
             unsigned cls;  // class bytes of the lane's four columns in row n (byte k = column c0+k)
         };
-        auto load_row = [&](int n) {
+        // Operand pipeline: unit t is row (i_lo-1)+t; lane 0 asks the copy engine for r, p and the class record of
+        // the warp's window, STAGES units ahead; the bytes land in this warp's ring and flip the stage's mbarrier.
+        const int row0 = L.i_lo - 1, nunits = L.i_hi - L.i_lo + 3;
+        unsigned char *ring = dyn_smem + (size_t)L.warp * STAGES * K1_STAGE_BYTES;
+        const unsigned ring_s = smem_u32(ring), bar_s = smem_u32(&s_bar[L.warp][0]);
+        const double *r_src = A.r + L.s, *q_src = A.p_old + L.s;
+        const unsigned char *c_src = A.cls + cls_index(g.cpitch, 0, L.wcol, 0);
+        auto issue = [&](int t) {
+            if (L.lane == 0 && t < nunits) {
+                const int st = t & (STAGES - 1);
+                const size_t n = (size_t)(row0 + t);
+                const unsigned bar = bar_s + 8u * st, dst = ring_s + (unsigned)(st * K1_STAGE_BYTES);
+                mbar_expect_tx(bar, FIRST ? ROW_BYTES + CLS_WIN : K1_STAGE_BYTES);
+                bulk_g2s(dst, r_src + n * P, ROW_BYTES, bar);
+                if (!FIRST) bulk_g2s(dst + ROW_BYTES, q_src + n * P, ROW_BYTES, bar);
+                bulk_g2s(dst + 2 * ROW_BYTES, c_src + n * (size_t)g.cpitch, CLS_WIN, bar);
+            }
+        };
+        auto fetch = [&](int t) {
             RowIn in;
-            const size_t o = (size_t)n * P;
-            in.r = ldg4_nc(rb + o, L.ld_ok);
-            if (!FIRST) in.q = ldg4_nc(qb + o, L.ld_ok);
-            in.cls = L.ld_ok ? __ldg(reinterpret_cast<const unsigned *>(cb + o)) : 0u;
+            const int st = t & (STAGES - 1);
+            mbar_wait(bar_s + 8u * st, (unsigned)(t / STAGES) & 1u);
+            const unsigned char *base = ring + st * K1_STAGE_BYTES;
+            in.r = lds4(base, L.lane);
+            if (!FIRST) in.q = lds4(base + ROW_BYTES, L.lane);
+            in.cls = *reinterpret_cast<const unsigned *>(base + 2 * ROW_BYTES + 4 * L.lane);
+            __syncwarp();      // every lane has its copy: the stage may be refilled
+            issue(t + STAGES);
             return in;
         };
+#pragma unroll
+        for (int t = 0; t < STAGES; ++t) issue(t);
         auto p_update = [&](const RowIn &in, int n) {
             V4 z = precond4<SAFE>(in.r, in.cls, s_lut, Db + (size_t)n * P); // S4:559
             if (!FIRST) {
@@ -638,10 +729,10 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         };
 
         // rows i_lo-1 and i_lo: p' of both, and the flux through the face between them
-        RowIn in = load_row(L.i_lo - 1);
+        RowIn in = fetch(0);
         const V4 pm = p_update(in, L.i_lo - 1);
         if (L.i_lo == 1) st4_mask(pob, pm, L.pw); // ring row 0
-        in = load_row(L.i_lo);
+        in = fetch(1);
         V4 pc = p_update(in, L.i_lo);
         unsigned cls_c = in.cls;
         st4_mask(pob + (size_t)L.i_lo * P, pc, L.pw);
@@ -671,18 +762,10 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
             cls_c = cur.cls;
         };
 
-        // The operands of row i+2 are requested before row i is computed. Deeper software prefetch does not
-        // pay (measured): a warp has six scoreboard slots, so waiting for the oldest row also waits for newer
-        // ones; latency is hidden by running many warps per SM instead.
         const unsigned last = (L.i_hi == g.nx) ? L.pw : 0u; // row i_hi+1 belongs to the next segment unless it is ring row nx+1
-        RowIn nxt = load_row(L.i_lo + 1);
 #pragma unroll 1
-        for (int i = L.i_lo; i < L.i_hi; ++i) {
-            const RowIn cur = nxt;
-            nxt = load_row(i + 2);
-            row_step(i, cur, L.pw);
-        }
-        row_step(L.i_hi, nxt, last);
+        for (int i = L.i_lo; i < L.i_hi; ++i) row_step(i, fetch(i - L.i_lo + 2), L.pw);
+        row_step(L.i_hi, fetch(L.i_hi - L.i_lo + 2), last);
     }
     if (bad) ctl->fault = 1;
 
@@ -729,11 +812,19 @@ __device__ __forceinline__ void finalize_iteration(Ctl *ctl, const Consts &c, do
 template <bool SAFE>
 __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2Args A) {
     Ctl *ctl = A.ctl;
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ __align__(8) unsigned long long s_bar[K1_WARPS][STAGES];
     __shared__ double2 s_lut[16];
     if (stopped(ctl)) return;
-    if (threadIdx.x < 16) s_lut[threadIdx.x] = make_double2(A.c.lutD[threadIdx.x], A.c.lutR[threadIdx.x]);
-    __syncthreads();
     const Geom g = A.g;
+    const Lane L = make_lane(g, A.rows_per_seg);
+    if (threadIdx.x < 16) s_lut[threadIdx.x] = make_double2(A.c.lutD[threadIdx.x], A.c.lutR[threadIdx.x]);
+    if (L.lane == 0) {
+#pragma unroll
+        for (int st = 0; st < STAGES; ++st) mbar_init(smem_u32(&s_bar[L.warp][st]), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
     const double denom = A.c.multi ? ctl->red[0] : ctl->denom;
     const bool brk = (A.c.norm_mode == 1) ? (denom < 1e-15) : (fabs(denom) < 1e-15); // S0:128 | S4:876
     if (brk) {
@@ -748,14 +839,12 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
     const double alpha = ctl->zr_old / denom; // S4:877
     const double h1 = A.c.h1, h2 = A.c.h2, rh1 = A.c.rh1, rh2 = A.c.rh2, mih1 = A.c.mih1, mih2 = A.c.mih2;
     const double inv_eps = A.c.inv_eps;
-    const Lane L = make_lane(g, A.rows_per_seg);
 
     double acc[2] = {0.0, 0.0};
     unsigned bad = 0u;
     if (L.s + 1 <= g.ny) {
         const size_t P = (size_t)g.pitch;
         const double *pb = A.p + L.c0, *ab = A.a + L.c0, *bb = A.b + L.c0, *Db = A.D + L.c0;
-        const unsigned char *cb = A.cls + L.c0;
         double *wb = A.w + L.c0, *rb = A.r + L.c0;
 
         struct RowIn {
@@ -763,20 +852,44 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
             unsigned cls;  // classes of row i+1
             V4 w, r;       // row i
         };
-        auto load_row = [&](int i) {
+        // Operand pipeline (see k1_kernel): unit t = row i_lo+t brings p'(i+1), w(i), r(i) and the classes of row i+1.
+        const int nunits = L.i_hi - L.i_lo + 1;
+        unsigned char *ring = dyn_smem + (size_t)L.warp * STAGES * K2_STAGE_BYTES;
+        const unsigned ring_s = smem_u32(ring), bar_s = smem_u32(&s_bar[L.warp][0]);
+        const double *p_src = A.p + L.s, *w_src = A.w + L.s, *r_src = A.r + L.s;
+        const unsigned char *c_src = A.cls + cls_index(g.cpitch, 0, L.wcol, 0);
+        auto issue = [&](int t) {
+            if (L.lane == 0 && t < nunits) {
+                const int st = t & (STAGES - 1);
+                const size_t i = (size_t)(L.i_lo + t);
+                const unsigned bar = bar_s + 8u * st, dst = ring_s + (unsigned)(st * K2_STAGE_BYTES);
+                mbar_expect_tx(bar, K2_STAGE_BYTES);
+                bulk_g2s(dst, p_src + (i + 1) * P, ROW_BYTES, bar);
+                bulk_g2s(dst + ROW_BYTES, w_src + i * P, ROW_BYTES, bar);
+                bulk_g2s(dst + 2 * ROW_BYTES, r_src + i * P, ROW_BYTES, bar);
+                bulk_g2s(dst + 3 * ROW_BYTES, c_src + (i + 1) * (size_t)g.cpitch, CLS_WIN, bar);
+            }
+        };
+        auto fetch = [&](int t) {
             RowIn in;
-            const size_t o = (size_t)i * P;
-            in.pn = ldg4_nc(pb + o + P, L.ld_ok);
-            in.cls = L.ld_ok ? __ldg(reinterpret_cast<const unsigned *>(cb + o + P)) : 0u;
-            in.w = ldg4(wb + o, L.ld_ok);
-            in.r = ldg4(rb + o, L.ld_ok);
+            const int st = t & (STAGES - 1);
+            mbar_wait(bar_s + 8u * st, (unsigned)(t / STAGES) & 1u);
+            const unsigned char *base = ring + st * K2_STAGE_BYTES;
+            in.pn = lds4(base, L.lane);
+            in.w = lds4(base + ROW_BYTES, L.lane);
+            in.r = lds4(base + 2 * ROW_BYTES, L.lane);
+            in.cls = *reinterpret_cast<const unsigned *>(base + 3 * ROW_BYTES + 4 * L.lane);
+            __syncwarp();
+            issue(t + STAGES);
             return in;
         };
+#pragma unroll
+        for (int t = 0; t < STAGES; ++t) issue(t);
 
         // rows i_lo-1 and i_lo of p', the classes of row i_lo, and the flux through the face between them
-        const V4 pm = ldg4_nc(pb + (size_t)(L.i_lo - 1) * P, L.ld_ok);
-        V4 pc = ldg4_nc(pb + (size_t)L.i_lo * P, L.ld_ok);
-        unsigned cls_c = L.ld_ok ? __ldg(reinterpret_cast<const unsigned *>(cb + (size_t)L.i_lo * P)) : 0u;
+        const V4 pm = ldg4_nc(pb + (size_t)(L.i_lo - 1) * P, true);
+        V4 pc = ldg4_nc(pb + (size_t)L.i_lo * P, true);
+        unsigned cls_c = __ldg(reinterpret_cast<const unsigned *>(A.cls + cls_index(g.cpitch, L.i_lo, L.wcol, 4 * L.lane)));
         V4 fxl;
         {
             const V4 nx = xface_numerators(pc, pm, cls_c, inv_eps, ab + (size_t)L.i_lo * P);
@@ -812,14 +925,8 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
             cls_c = cur.cls;
         };
 
-        RowIn nxt = load_row(L.i_lo);
 #pragma unroll 1
-        for (int i = L.i_lo; i < L.i_hi; ++i) {
-            const RowIn cur = nxt;
-            nxt = load_row(i + 1);
-            row_step(i, cur);
-        }
-        row_step(L.i_hi, nxt);
+        for (int i = L.i_lo; i <= L.i_hi; ++i) row_step(i, fetch(i - L.i_lo));
     }
     if (bad) ctl->fault = 1;
 

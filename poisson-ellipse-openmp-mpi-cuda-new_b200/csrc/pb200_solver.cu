@@ -104,6 +104,28 @@ Consts make_consts(const pb200_params &p) {
 
 int pitch_for(int ny) { return ((ny + 2 + 15) / 16) * 16; }
 
+// bytes per row of the class map: one 128-byte record per warp window, whole CTAs of windows
+int cpitch_for(int ny) {
+    const int wcols = (ny + K1_OWN - 1) / K1_OWN;
+    return ((wcols + K1_WARPS - 1) / K1_WARPS) * K1_WARPS * CLS_WIN;
+}
+
+// the iteration kernels stage their operands in dynamic shared memory (more than the 48 KB default for K2)
+pb200_status enable_kernel_smem() {
+    static thread_local int done_for_device = -1;
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (done_for_device == dev) return PB200_OK;
+    CK(cudaFuncSetAttribute(k1_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, K1_SMEM));
+    CK(cudaFuncSetAttribute(k1_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, K1_SMEM));
+    CK(cudaFuncSetAttribute(k1_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, K1_SMEM));
+    CK(cudaFuncSetAttribute(k1_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, K1_SMEM));
+    CK(cudaFuncSetAttribute(k2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, K2_SMEM));
+    CK(cudaFuncSetAttribute(k2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, K2_SMEM));
+    done_for_device = dev;
+    return PB200_OK;
+}
+
 bool coef_in_div_range(double v) {
     const double a = std::fabs(v);
     return a == 0.0 || (a >= 0x1p-400 && a <= 0x1p400);
@@ -126,9 +148,17 @@ void Fields::release() {
 pb200_status Fields::allocate(const Geom &geom) {
     g = geom;
     elems = static_cast<size_t>(g.nx + 2) * static_cast<size_t>(g.pitch);
+    // The last warp window of a row may reach past the pitch: the bulk copies then read on into the next row, and
+    // past the last row into this zeroed slack.
+    const size_t slack = 2 * K1_WIN;
     double **all[] = {&a, &b, &D, &w, &r, &p[0], &p[1]};
-    for (double **q : all) CK(cudaMalloc(q, elems * sizeof(double)));
-    CK(cudaMalloc(&cls, elems));
+    for (double **q : all) {
+        CK(cudaMalloc(q, (elems + slack) * sizeof(double)));
+        CK(cudaMemset(*q + elems, 0, slack * sizeof(double)));
+    }
+    cls_bytes = static_cast<size_t>(g.nx + 2) * static_cast<size_t>(g.cpitch);
+    CK(cudaMalloc(&cls, cls_bytes));
+    CK(cudaMemset(cls, 0, cls_bytes));
     return PB200_OK;
 }
 
@@ -194,6 +224,7 @@ pb200_status Solver::create(const pb200_params &params) {
     g.nx = i1 - i0 + 1;
     g.ny = j1 - j0 + 1;
     g.pitch = pitch_for(g.ny);
+    g.cpitch = cpitch_for(g.ny);
     g.gi0 = i0 - 1;
     g.gj0 = j0 - 1;
     g.M = prm.M;
@@ -202,6 +233,8 @@ pb200_status Solver::create(const pb200_params &params) {
     // the coefficients are 1, 1/eps or a blend of the two (S4:167-177): div_const's fast path needs them in range
     safe_div = !(coef_in_div_range(1.0 / c.eps) && coef_in_div_range(c.eps) && coef_in_div_range(c.f_val));
     CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    st = enable_kernel_smem();
+    if (st != PB200_OK) return st;
     st = f.allocate(g);
     if (st != PB200_OK) return st;
     plan_launch();
@@ -274,17 +307,17 @@ K2Args Solver::k2_args(long long k) const {
 
 void Solver::launch_k1(const K1Args &a, bool first) {
     if (first) {
-        if (safe_div) k1_kernel<true, true><<<k1_grid, K1_THREADS, 0, stream>>>(a);
-        else k1_kernel<true, false><<<k1_grid, K1_THREADS, 0, stream>>>(a);
+        if (safe_div) k1_kernel<true, true><<<k1_grid, K1_THREADS, K1_SMEM, stream>>>(a);
+        else k1_kernel<true, false><<<k1_grid, K1_THREADS, K1_SMEM, stream>>>(a);
     } else {
-        if (safe_div) k1_kernel<false, true><<<k1_grid, K1_THREADS, 0, stream>>>(a);
-        else k1_kernel<false, false><<<k1_grid, K1_THREADS, 0, stream>>>(a);
+        if (safe_div) k1_kernel<false, true><<<k1_grid, K1_THREADS, K1_SMEM, stream>>>(a);
+        else k1_kernel<false, false><<<k1_grid, K1_THREADS, K1_SMEM, stream>>>(a);
     }
 }
 
 void Solver::launch_k2(const K2Args &a) {
-    if (safe_div) k2_kernel<true><<<k2_grid, K2_THREADS, 0, stream>>>(a);
-    else k2_kernel<false><<<k2_grid, K2_THREADS, 0, stream>>>(a);
+    if (safe_div) k2_kernel<true><<<k2_grid, K2_THREADS, K2_SMEM, stream>>>(a);
+    else k2_kernel<false><<<k2_grid, K2_THREADS, K2_SMEM, stream>>>(a);
 }
 
 void Solver::launch_init() {

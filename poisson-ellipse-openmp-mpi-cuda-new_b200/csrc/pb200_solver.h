@@ -23,6 +23,8 @@ pb200_status validate(const pb200_params &p);
 Consts make_consts(const pb200_params &p);
 bool coef_in_div_range(double v); // zero, or 2^-400 <= |v| <= 2^400
 int pitch_for(int ny);
+int cpitch_for(int ny);
+pb200_status enable_kernel_smem();
 
 // The device arrays of one block. Hot (touched every iteration): w, r, p[0], p[1] (ping-pong) and one class
 // byte per cell. Cold (written once by setup, read only on cells cut by the ellipse): a, b, D.
@@ -31,7 +33,8 @@ struct Fields {
     Geom g{};
     size_t elems = 0;
     double *a = nullptr, *b = nullptr, *D = nullptr, *w = nullptr, *r = nullptr, *p[2] = {nullptr, nullptr};
-    unsigned char *cls = nullptr; // one class byte per stored cell (pb200_kernels.cuh)
+    unsigned char *cls = nullptr; // class bytes, one 128-byte record per warp window and row (pb200_kernels.cuh)
+    size_t cls_bytes = 0;
     ~Fields();
     pb200_status allocate(const Geom &geom);
     void release();
