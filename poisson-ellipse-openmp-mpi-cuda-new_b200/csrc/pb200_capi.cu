@@ -26,7 +26,7 @@ struct OpBlock {
     double *Ap = nullptr; // A p' as K1 computes it (the solver never stores it)
     cudaStream_t stream = nullptr;
     dim3 k1_grid, k2_grid, init_grid;
-    int rows_per_seg = 8;
+    int wn = 1;
     bool safe_div = false;
 
     ~OpBlock() {
@@ -67,8 +67,10 @@ struct OpBlock {
         if (st != PB200_OK) return st;
         CK(cudaMalloc(&Ap, f.elems * sizeof(double)));
         for (double *q : {f.a, f.b, f.D, f.w, f.r, f.p[0], f.p[1], Ap}) CK(cudaMemset(q, 0, f.elems * sizeof(double)));
-        const int wcols = (ny + K1_OWN - 1) / K1_OWN;
-        k1_grid = dim3((wcols + K1_WARPS - 1) / K1_WARPS, (nx + rows_per_seg - 1) / rows_per_seg, 1);
+        wn = (ny + K1_OWN - 1) / K1_OWN;
+        // small pieces on purpose (3 rows per warp) so that the tests cross many piece and window boundaries
+        const long long T = (long long)wn * nx;
+        k1_grid = dim3(std::max((wn + K1_WARPS - 1) / K1_WARPS, (int)std::min<long long>(1024, (T + 3LL * K1_WARPS - 1) / (3LL * K1_WARPS))), 1, 1);
         k2_grid = k1_grid;
         init_grid = dim3((ny + INIT_THREADS - 1) / INIT_THREADS, std::min(nx, 1024), 1);
         size_t nb = (size_t)k1_grid.x * k1_grid.y;
@@ -142,7 +144,7 @@ struct OpBlock {
         a.ctl = ctl;
         a.g = f.g;
         a.c = c;
-        a.rows_per_seg = rows_per_seg;
+        a.wn = wn;
         if (first) {
             if (safe_div) k1_kernel<true, true><<<k1_grid, K1_THREADS, K1_SMEM>>>(a);
             else k1_kernel<true, false><<<k1_grid, K1_THREADS, K1_SMEM>>>(a);
@@ -166,7 +168,7 @@ struct OpBlock {
         a.ctl = ctl;
         a.g = f.g;
         a.c = c;
-        a.rows_per_seg = rows_per_seg;
+        a.wn = wn;
         if (safe_div) k2_kernel<true><<<k2_grid, K2_THREADS, K2_SMEM>>>(a);
         else k2_kernel<false><<<k2_grid, K2_THREADS, K2_SMEM>>>(a);
         CK(cudaGetLastError());

@@ -414,7 +414,7 @@ struct K1Args {
     Ctl *ctl;
     Geom g;
     Consts c;
-    int rows_per_seg;
+    int wn; // warp windows per row: ceil(ny / 124)
 };
 
 struct K2Args {
@@ -427,7 +427,7 @@ struct K2Args {
     Ctl *ctl;
     Geom g;
     Consts c;
-    int rows_per_seg;
+    int wn;
 };
 
 struct V4 {
@@ -518,15 +518,34 @@ struct Lane {
     unsigned pw;   // bit k: column c0+k gets this lane's p' (owned interior cells + ring columns)
 };
 
-__device__ __forceinline__ Lane make_lane(const Geom &g, int rows_per_seg) {
+// Work partition. The rows are cut into NB = floor(warps / windows) bands of equal height (+-1 row) and warp gw
+// takes window gw % windows of band gw / windows: warps that run side by side read side-by-side windows of the same
+// rows (DRAM page locality). The host sizes the grid so that a band is about 20 rows (solver.cu: march_blocks).
+struct Part {
+    int nsub;                  // 0 or 1 sub-segments (kept as a list: the kernels loop over it)
+    int wcol[1], lo[1], hi[1]; // window and inclusive row range
+};
+
+__device__ __forceinline__ Part make_part(int gw, int nw, int wn, int nx) {
+    Part p;
+    const int nb = max(1, nw / wn);
+    const int b = gw / wn;
+    p.wcol[0] = gw - b * wn;
+    p.lo[0] = 1 + (int)(((long long)nx * b) / nb);
+    p.hi[0] = (int)(((long long)nx * (b + 1)) / nb);
+    p.nsub = (b < nb && p.lo[0] <= p.hi[0]) ? 1 : 0;
+    return p;
+}
+
+__device__ __forceinline__ Lane make_lane(const Geom &g, int lane, int warp, int wcol, int i_lo, int i_hi) {
     Lane L;
-    L.lane = threadIdx.x & 31;
-    L.warp = threadIdx.x >> 5;
-    L.wcol = blockIdx.x * K1_WARPS + L.warp;
+    L.lane = lane;
+    L.warp = warp;
+    L.wcol = wcol;
     L.s = L.wcol * K1_OWN;
     L.c0 = L.s + LW * L.lane;
-    L.i_lo = 1 + blockIdx.y * rows_per_seg;
-    L.i_hi = min(g.nx, L.i_lo + rows_per_seg - 1);
+    L.i_lo = i_lo;
+    L.i_hi = i_hi;
     L.ld_ok = (L.c0 + LW - 1 < g.pitch);
     L.own = 0u;
     L.pw = 0u;
@@ -663,21 +682,25 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
     __shared__ double2 s_lut[16];
     if (stopped(ctl)) return;
     const Geom g = A.g;
-    const Lane L = make_lane(g, A.rows_per_seg);
+    const int lane_id = threadIdx.x & 31, warp_id = threadIdx.x >> 5;
     if (threadIdx.x < 16) s_lut[threadIdx.x] = make_double2(A.c.lutD[threadIdx.x], A.c.lutR[threadIdx.x]);
-    if (L.lane == 0) {
+    if (lane_id == 0) {
 #pragma unroll
-        for (int st = 0; st < STAGES; ++st) mbar_init(smem_u32(&s_bar[L.warp][st]), 1);
+        for (int st = 0; st < STAGES; ++st) mbar_init(smem_u32(&s_bar[warp_id][st]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     const double h1 = A.c.h1, h2 = A.c.h2, rh1 = A.c.rh1, rh2 = A.c.rh2, mih1 = A.c.mih1, mih2 = A.c.mih2;
     const double inv_eps = A.c.inv_eps;
     const double beta = FIRST ? 0.0 : ctl->beta;
+    const Part part = make_part(blockIdx.x * K1_WARPS + warp_id, gridDim.x * K1_WARPS, A.wn, g.nx);
 
     double acc[1] = {0.0};
     unsigned bad = 0u;
-    if (L.s + 1 <= g.ny) { // warp-uniform: this warp owns at least one interior column
+    unsigned tcount = 0u; // pipeline units consumed so far by this warp: stage and mbarrier parity follow from it
+#pragma unroll 1
+    for (int sub = 0; sub < part.nsub; ++sub) {
+        const Lane L = make_lane(g, lane_id, warp_id, part.wcol[sub], part.lo[sub], part.hi[sub]);
         const size_t P = (size_t)g.pitch;
         const double *ab = A.a + L.c0, *bb = A.b + L.c0, *Db = A.D + L.c0;
         double *pob = A.p_new + L.c0;
@@ -696,7 +719,7 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         const unsigned char *c_src = A.cls + cls_index(g.cpitch, 0, L.wcol, 0);
         auto issue = [&](int t) {
             if (L.lane == 0 && t < nunits) {
-                const int st = t & (STAGES - 1);
+                const int st = (int)((tcount + (unsigned)t) & (STAGES - 1));
                 const size_t n = (size_t)(row0 + t);
                 const unsigned bar = bar_s + 8u * st, dst = ring_s + (unsigned)(st * K1_STAGE_BYTES);
                 mbar_expect_tx(bar, FIRST ? ROW_BYTES + CLS_WIN : K1_STAGE_BYTES);
@@ -707,8 +730,9 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         };
         auto fetch = [&](int t) {
             RowIn in;
-            const int st = t & (STAGES - 1);
-            mbar_wait(bar_s + 8u * st, (unsigned)(t / STAGES) & 1u);
+            const unsigned u = tcount + (unsigned)t;
+            const int st = (int)(u & (STAGES - 1));
+            mbar_wait(bar_s + 8u * st, (u / STAGES) & 1u);
             const unsigned char *base = ring + st * K1_STAGE_BYTES;
             in.r = lds4(base, L.lane);
             if (!FIRST) in.q = lds4(base + ROW_BYTES, L.lane);
@@ -766,6 +790,7 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
 #pragma unroll 1
         for (int i = L.i_lo; i < L.i_hi; ++i) row_step(i, fetch(i - L.i_lo + 2), L.pw);
         row_step(L.i_hi, fetch(L.i_hi - L.i_lo + 2), last);
+        tcount += (unsigned)nunits;
     }
     if (bad) ctl->fault = 1;
 
@@ -817,18 +842,18 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
     __shared__ double2 s_lut[16];
     if (stopped(ctl)) return;
     const Geom g = A.g;
-    const Lane L = make_lane(g, A.rows_per_seg);
+    const int lane_id = threadIdx.x & 31, warp_id = threadIdx.x >> 5;
     if (threadIdx.x < 16) s_lut[threadIdx.x] = make_double2(A.c.lutD[threadIdx.x], A.c.lutR[threadIdx.x]);
-    if (L.lane == 0) {
+    if (lane_id == 0) {
 #pragma unroll
-        for (int st = 0; st < STAGES; ++st) mbar_init(smem_u32(&s_bar[L.warp][st]), 1);
+        for (int st = 0; st < STAGES; ++st) mbar_init(smem_u32(&s_bar[warp_id][st]), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     const double denom = A.c.multi ? ctl->red[0] : ctl->denom;
     const bool brk = (A.c.norm_mode == 1) ? (denom < 1e-15) : (fabs(denom) < 1e-15); // S0:128 | S4:876
     if (brk) {
-        if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
             ctl->denom = denom;
             ctl->status = STOP_DENOM;
             __threadfence();
@@ -840,9 +865,14 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
     const double h1 = A.c.h1, h2 = A.c.h2, rh1 = A.c.rh1, rh2 = A.c.rh2, mih1 = A.c.mih1, mih2 = A.c.mih2;
     const double inv_eps = A.c.inv_eps;
 
+    const Part part = make_part(blockIdx.x * K1_WARPS + warp_id, gridDim.x * K1_WARPS, A.wn, g.nx);
+
     double acc[2] = {0.0, 0.0};
     unsigned bad = 0u;
-    if (L.s + 1 <= g.ny) {
+    unsigned tcount = 0u;
+#pragma unroll 1
+    for (int sub = 0; sub < part.nsub; ++sub) {
+        const Lane L = make_lane(g, lane_id, warp_id, part.wcol[sub], part.lo[sub], part.hi[sub]);
         const size_t P = (size_t)g.pitch;
         const double *pb = A.p + L.c0, *ab = A.a + L.c0, *bb = A.b + L.c0, *Db = A.D + L.c0;
         double *wb = A.w + L.c0, *rb = A.r + L.c0;
@@ -860,7 +890,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         const unsigned char *c_src = A.cls + cls_index(g.cpitch, 0, L.wcol, 0);
         auto issue = [&](int t) {
             if (L.lane == 0 && t < nunits) {
-                const int st = t & (STAGES - 1);
+                const int st = (int)((tcount + (unsigned)t) & (STAGES - 1));
                 const size_t i = (size_t)(L.i_lo + t);
                 const unsigned bar = bar_s + 8u * st, dst = ring_s + (unsigned)(st * K2_STAGE_BYTES);
                 mbar_expect_tx(bar, K2_STAGE_BYTES);
@@ -872,8 +902,9 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         };
         auto fetch = [&](int t) {
             RowIn in;
-            const int st = t & (STAGES - 1);
-            mbar_wait(bar_s + 8u * st, (unsigned)(t / STAGES) & 1u);
+            const unsigned u = tcount + (unsigned)t;
+            const int st = (int)(u & (STAGES - 1));
+            mbar_wait(bar_s + 8u * st, (u / STAGES) & 1u);
             const unsigned char *base = ring + st * K2_STAGE_BYTES;
             in.pn = lds4(base, L.lane);
             in.w = lds4(base + ROW_BYTES, L.lane);
@@ -927,6 +958,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
 
 #pragma unroll 1
         for (int i = L.i_lo; i <= L.i_hi; ++i) row_step(i, fetch(i - L.i_lo));
+        tcount += (unsigned)nunits;
     }
     if (bad) ctl->fault = 1;
 
