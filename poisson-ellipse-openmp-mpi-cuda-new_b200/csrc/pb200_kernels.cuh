@@ -90,7 +90,6 @@ struct Ctl {
     double red[4];   // [0] denom (this rank) [1] sum dw^2 (this rank, unweighted) [2] (z,r) (this rank) -- all-reduced in place when multi
     long long iter;  // S4:848
     int done;        // loop has ended; later kernels return immediately
-    int fault;       // a value left the range of the unchecked fast divisions: results are void, rerun SAFE
     int status;      // PB200_STOP_*
     int conv_iter;   // first k with diff < delta
     unsigned int ticket[2];
@@ -292,12 +291,16 @@ __global__ void __launch_bounds__(256) diag_kernel(Geom g, Consts c, const doubl
 // ------------------------------------------------------------------------------------------
 // Division helpers for the iteration kernels.
 
-// True when v is zero or 2^-400 <= |v| <= 2^400: products of such values with coefficients in the same
-// range stay inside the interval where div_const's residuals are exact. Integer pipe only.
+// True when v is zero or 2^-840 <= |v| < 2^601. For such p' and r, with coefficients in 2^-50..2^300 and grid
+// steps in 2^-100..2^10 (checked on the host, else the SAFE kernels run), every numerator x of a fast division is 0
+// or 2^-943 <= |x| <= 2^901: the residual x - h*q of div_const is then exactly representable (needs |x| >= 2^-970)
+// and no intermediate overflows, so the two-correction quotient is the IEEE quotient. Values outside the window
+// DO occur in this problem -- the iterates decay by about a factor 4 per cell into the penalised exterior until they
+// underflow -- so rows that contain one take the IEEE-divide path (a thin ring of the grid). Integer pipe only.
 __device__ __forceinline__ bool in_div_range(double v) {
     const unsigned hi = (unsigned)__double2hiint(v) & 0x7fffffffu;
     const unsigned e = hi >> 20;
-    return (e - 623u <= 800u) || ((hi | (unsigned)__double2loint(v)) == 0u);
+    return (e - 183u <= 1440u) || ((hi | (unsigned)__double2loint(v)) == 0u);
 }
 
 // div_const without the per-call range test (the caller has established the range).
@@ -372,8 +375,8 @@ __global__ void __launch_bounds__(INIT_THREADS) init_kernel(const InitArgs A) {
 // warp-uniform fast paths for rows that lie wholly inside or wholly outside the ellipse.
 //
 // Divisions: the fast kernels (SAFE = false) use the exact-residual scheme of div_const without per-call
-// range tests; every p' and every new r is range-tested once (integer pipe) and a hit raises Ctl::fault,
-// upon which the host repeats the solve with the SAFE kernels (IEEE divides everywhere).
+// range tests; instead every p' and every r is range-tested once per row (integer pipe, see in_div_range) and
+// a warp whose row holds a value outside the proven window computes that row with IEEE divides.
 
 constexpr int LW = 4;                  // columns per lane
 constexpr int K1_WIN = 32 * LW;        // window per warp
@@ -493,21 +496,9 @@ __device__ __forceinline__ void st4_mask(double *p, const V4 &x, const unsigned 
 
 __device__ __forceinline__ double class_value(unsigned k, double inv_eps) { return (k & 1u) ? inv_eps : 1.0; }
 
-// 1 when a value is outside the range in which the unchecked exact-residual divisions are proven (see in_div_range)
-__device__ __forceinline__ unsigned range_fault4(const V4 &x) {
-    return (unsigned)!(in_div_range(x.v[0]) && in_div_range(x.v[1]) && in_div_range(x.v[2]) && in_div_range(x.v[3]));
-}
-// the same, looking only at the elements whose mask bit is set
-__device__ __forceinline__ unsigned range_fault4(const V4 &x, const unsigned mask) {
-    unsigned bad = 0u;
-#pragma unroll
-    for (int k = 0; k < LW; ++k) bad |= (unsigned)(((mask >> k) & 1u) && !in_div_range(x.v[k]));
-    return bad;
-}
-
-template <bool SAFE>
-__device__ __forceinline__ double div_h(double x, double h, double rh) {
-    return SAFE ? __ddiv_rn(x, h) : div_const_nocheck(x, h, rh);
+// true when one of the four values is outside the window in which the fast divisions are proven (in_div_range)
+__device__ __forceinline__ bool range_bad4(const V4 &x) {
+    return !(in_div_range(x.v[0]) && in_div_range(x.v[1]) && in_div_range(x.v[2]) && in_div_range(x.v[3]));
 }
 
 // What a lane knows about its place in the march (computed once per kernel).
@@ -632,17 +623,23 @@ __device__ __forceinline__ V4 precond4(const V4 &r, const unsigned cls, const do
     V4 z;
     const unsigned kd = (cls >> 4) & 0x0f0f0f0fu;
     const unsigned k0 = __shfl_sync(0xffffffffu, kd, 0) & 0xfu;
+    const bool slow = SAFE || __any_sync(0xffffffffu, range_bad4(r)); // a value outside the proven window: IEEE divides
     if (__all_sync(0xffffffffu, kd == k0 * 0x01010101u) && k0 != DCLS_GENERAL) {
         const double2 DR = s_lut[k0];
+        if (slow) {
 #pragma unroll
-        for (int k = 0; k < LW; ++k) z.v[k] = SAFE ? precond_div(r.v[k], DR.x) : div_const_nocheck(r.v[k], DR.x, DR.y);
+            for (int k = 0; k < LW; ++k) z.v[k] = precond_div(r.v[k], DR.x);
+        } else {
+#pragma unroll
+            for (int k = 0; k < LW; ++k) z.v[k] = div_const_nocheck(r.v[k], DR.x, DR.y);
+        }
         return z;
     }
 #pragma unroll
     for (int k = 0; k < LW; ++k) {
         const unsigned kk = (kd >> (8 * k)) & 0xfu;
         const double2 DR = s_lut[kk];
-        z.v[k] = SAFE ? precond_div(r.v[k], DR.x) : div_const_nocheck(r.v[k], DR.x, DR.y);
+        z.v[k] = slow ? precond_div(r.v[k], DR.x) : div_const_nocheck(r.v[k], DR.x, DR.y);
         if (kk == DCLS_GENERAL) z.v[k] = precond_div(r.v[k], __ldg(D_row + k));
     }
     return z;
@@ -650,13 +647,22 @@ __device__ __forceinline__ V4 precond4(const V4 &r, const unsigned cls, const do
 
 // Stencil of one row for a lane (S4:526-535), given the face numerators. Updates the carried x flux.
 template <bool SAFE>
-__device__ __forceinline__ V4 stencil_row(const V4 &nx, const V4 &ny, V4 &fxl, const double h1, const double rh1,
-                                          const double h2, const double rh2, const double mih1, const double mih2) {
+__device__ __forceinline__ V4 stencil_row(const V4 &nx, const V4 &ny, V4 &fxl, const bool slow, const double h1,
+                                          const double rh1, const double h2, const double rh2, const double mih1,
+                                          const double mih2) {
     V4 fx, fy, out;
+    if (SAFE || slow) { // warp-uniform
 #pragma unroll
-    for (int k = 0; k < LW; ++k) {
-        fx.v[k] = div_h<SAFE>(nx.v[k], h1, rh1);
-        fy.v[k] = div_h<SAFE>(ny.v[k], h2, rh2);
+        for (int k = 0; k < LW; ++k) {
+            fx.v[k] = __ddiv_rn(nx.v[k], h1);
+            fy.v[k] = __ddiv_rn(ny.v[k], h2);
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < LW; ++k) {
+            fx.v[k] = div_const_nocheck(nx.v[k], h1, rh1);
+            fy.v[k] = div_const_nocheck(ny.v[k], h2, rh2);
+        }
     }
     const double fl = shfl_up1(fy.v[LW - 1]); // Fy left of the lane's first column = previous lane's last face
 #pragma unroll
@@ -668,9 +674,7 @@ __device__ __forceinline__ V4 stencil_row(const V4 &nx, const V4 &ny, V4 &fxl, c
     return out;
 }
 
-__device__ __forceinline__ bool stopped(const Ctl *ctl) {
-    return (*reinterpret_cast<const volatile int *>(&ctl->done) | *reinterpret_cast<const volatile int *>(&ctl->fault)) != 0;
-}
+__device__ __forceinline__ bool stopped(const Ctl *ctl) { return *reinterpret_cast<const volatile int *>(&ctl->done) != 0; }
 
 // FIRST: iteration 1, p' = z (S4:830). SAFE: IEEE divides everywhere (coefficients or data outside the range in
 // which the exact-residual divisions are proven).
@@ -696,7 +700,6 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
     const Part part = make_part(blockIdx.x * K1_WARPS + warp_id, gridDim.x * K1_WARPS, A.wn, g.nx);
 
     double acc[1] = {0.0};
-    unsigned bad = 0u;
     unsigned tcount = 0u; // pipeline units consumed so far by this warp: stage and mbarrier parity follow from it
 #pragma unroll 1
     for (int sub = 0; sub < part.nsub; ++sub) {
@@ -737,7 +740,11 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
             in.r = lds4(base, L.lane);
             if (!FIRST) in.q = lds4(base + ROW_BYTES, L.lane);
             in.cls = *reinterpret_cast<const unsigned *>(base + 2 * ROW_BYTES + 4 * L.lane);
-            __syncwarp();      // every lane has its copy: the stage may be refilled
+            // Every lane has its copy; the stage may be refilled. The refill is written by the async proxy: without
+            // the proxy fence it may overtake the generic-proxy reads above (observed: wrong, run-to-run varying
+            // results on long solves).
+            __syncwarp();
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             issue(t + STAGES);
             return in;
         };
@@ -760,25 +767,32 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         V4 pc = p_update(in, L.i_lo);
         unsigned cls_c = in.cls;
         st4_mask(pob + (size_t)L.i_lo * P, pc, L.pw);
-        if (!SAFE) bad |= range_fault4(pm) | range_fault4(pc);
+        bool bad_c = !SAFE && (range_bad4(pm) || range_bad4(pc));
         V4 fxl;
         {
             const V4 nx = xface_numerators(pc, pm, cls_c, inv_eps, ab + (size_t)L.i_lo * P);
+            if (SAFE || __any_sync(0xffffffffu, bad_c)) {
 #pragma unroll
-            for (int k = 0; k < LW; ++k) fxl.v[k] = div_h<SAFE>(nx.v[k], h1, rh1);
+                for (int k = 0; k < LW; ++k) fxl.v[k] = __ddiv_rn(nx.v[k], h1);
+            } else {
+#pragma unroll
+                for (int k = 0; k < LW; ++k) fxl.v[k] = div_const_nocheck(nx.v[k], h1, rh1);
+            }
         }
 
         // one row: consumes the operands of row i+1, leaves p'(i+1), Fx(i+1/2) and the classes of row i+1
         auto row_step = [&](const int i, const RowIn &cur, const unsigned st_mask) {
             const V4 pn = p_update(cur, i + 1);
             st4_mask(pob + (size_t)(i + 1) * P, pn, st_mask);
-            if (!SAFE) bad |= range_fault4(pn);
+            const bool bad_n = !SAFE && range_bad4(pn);
+            const bool slow = __any_sync(0xffffffffu, bad_c | bad_n);
+            bad_c = bad_n;
             const double pr = shfl_dn1(pc.v[0]); // right neighbour of the lane's last column
             const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
             V4 nx, ny;
             flux_numerators(pn, pc, pr, cur.cls, cls_c, cls_r, L.lane, inv_eps, ab + (size_t)(i + 1) * P,
                             bb + (size_t)i * P, nx, ny);
-            const V4 out = stencil_row<SAFE>(nx, ny, fxl, h1, rh1, h2, rh2, mih1, mih2);
+            const V4 out = stencil_row<SAFE>(nx, ny, fxl, slow, h1, rh1, h2, rh2, mih1, mih2);
             if (apb) st4_mask(apb + (size_t)i * P, out, L.own);
 #pragma unroll
             for (int k = 0; k < LW; ++k) acc[0] += ((L.own >> k) & 1u) ? out.v[k] * pc.v[k] : 0.0; // S4:594
@@ -792,12 +806,10 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         row_step(L.i_hi, fetch(L.i_hi - L.i_lo + 2), last);
         tcount += (unsigned)nunits;
     }
-    if (bad) ctl->fault = 1;
 
     double tot[1];
     if (grid_reduce<1, K1_THREADS>(acc, A.partials, &ctl->ticket[0], tot)) {
         ctl->red[0] = tot[0] * h1 * h2; // S3:191: sum * h1 * h2
-        ctl->red[3] = (double)*reinterpret_cast<volatile int *>(&ctl->fault);
         ctl->iter = ctl->iter + 1;      // S4:847-848: k
         if (!A.c.multi) ctl->denom = ctl->red[0];
     }
@@ -868,7 +880,6 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
     const Part part = make_part(blockIdx.x * K1_WARPS + warp_id, gridDim.x * K1_WARPS, A.wn, g.nx);
 
     double acc[2] = {0.0, 0.0};
-    unsigned bad = 0u;
     unsigned tcount = 0u;
 #pragma unroll 1
     for (int sub = 0; sub < part.nsub; ++sub) {
@@ -910,7 +921,8 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
             in.w = lds4(base + ROW_BYTES, L.lane);
             in.r = lds4(base + 2 * ROW_BYTES, L.lane);
             in.cls = *reinterpret_cast<const unsigned *>(base + 3 * ROW_BYTES + 4 * L.lane);
-            __syncwarp();
+            __syncwarp(); // see k1_kernel: reads first, proxy fence, then the refill
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             issue(t + STAGES);
             return in;
         };
@@ -921,27 +933,35 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         const V4 pm = ldg4_nc(pb + (size_t)(L.i_lo - 1) * P, true);
         V4 pc = ldg4_nc(pb + (size_t)L.i_lo * P, true);
         unsigned cls_c = __ldg(reinterpret_cast<const unsigned *>(A.cls + cls_index(g.cpitch, L.i_lo, L.wcol, 4 * L.lane)));
+        bool bad_c = !SAFE && (range_bad4(pm) || range_bad4(pc));
         V4 fxl;
         {
             const V4 nx = xface_numerators(pc, pm, cls_c, inv_eps, ab + (size_t)L.i_lo * P);
+            if (SAFE || __any_sync(0xffffffffu, bad_c)) {
 #pragma unroll
-            for (int k = 0; k < LW; ++k) fxl.v[k] = div_h<SAFE>(nx.v[k], h1, rh1);
+                for (int k = 0; k < LW; ++k) fxl.v[k] = __ddiv_rn(nx.v[k], h1);
+            } else {
+#pragma unroll
+                for (int k = 0; k < LW; ++k) fxl.v[k] = div_const_nocheck(nx.v[k], h1, rh1);
+            }
         }
 
         auto row_step = [&](const int i, const RowIn &cur) {
+            const bool bad_n = !SAFE && range_bad4(cur.pn);
+            const bool slow = __any_sync(0xffffffffu, bad_c | bad_n);
+            bad_c = bad_n;
             const double pr = shfl_dn1(pc.v[0]);
             const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
             V4 nx, ny;
             flux_numerators(cur.pn, pc, pr, cur.cls, cls_c, cls_r, L.lane, inv_eps, ab + (size_t)(i + 1) * P,
                             bb + (size_t)i * P, nx, ny);
-            const V4 Ap = stencil_row<SAFE>(nx, ny, fxl, h1, rh1, h2, rh2, mih1, mih2); // the expressions K1 used for (Ap,p)
+            const V4 Ap = stencil_row<SAFE>(nx, ny, fxl, slow, h1, rh1, h2, rh2, mih1, mih2); // the expressions K1 used for (Ap,p)
             V4 wn, rn;
 #pragma unroll
             for (int k = 0; k < LW; ++k) {
                 wn.v[k] = cur.w.v[k] + alpha * pc.v[k]; // S4:647
                 rn.v[k] = cur.r.v[k] - alpha * Ap.v[k]; // S4:648
             }
-            if (!SAFE) bad |= range_fault4(rn, L.own);
             const V4 zn = precond4<SAFE>(rn, cls_c, s_lut, Db + (size_t)i * P); // S4:559
 #pragma unroll
             for (int k = 0; k < LW; ++k) {
@@ -960,27 +980,21 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         for (int i = L.i_lo; i <= L.i_hi; ++i) row_step(i, fetch(i - L.i_lo));
         tcount += (unsigned)nunits;
     }
-    if (bad) ctl->fault = 1;
 
     double tot[2];
     if (grid_reduce<2, K2_THREADS>(acc, A.partials, &ctl->ticket[1], tot)) {
         const double zr = tot[1] * A.c.h1 * A.c.h2; // S3:191
         ctl->red[1] = tot[0];
         ctl->red[2] = zr;
-        ctl->red[3] = (double)*reinterpret_cast<volatile int *>(&ctl->fault);
-        if (!A.c.multi && ctl->red[3] == 0.0) finalize_iteration(ctl, A.c, A.trace, alpha, tot[0], zr);
+        if (!A.c.multi) finalize_iteration(ctl, A.c, A.trace, alpha, tot[0], zr);
     }
 }
 
-// Multi-GPU: after the all-reduce of red[1..3] (or red[2] at init) every rank runs the same scalar tail.
+// Multi-GPU: after the all-reduce of red[1..2] (or red[2] at init) every rank runs the same scalar tail.
 __global__ void finalize_kernel(Ctl *ctl, Consts c, double *trace, int init) {
     if (stopped(ctl)) return;
     if (init) {
         ctl->zr_old = ctl->red[2];
-        return;
-    }
-    if (ctl->red[3] != 0.0) { // some rank left the range of the fast divisions: every rank stops, the host restarts SAFE
-        ctl->fault = 1;
         return;
     }
     const double denom = ctl->red[0];

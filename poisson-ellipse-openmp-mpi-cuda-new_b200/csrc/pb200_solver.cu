@@ -127,9 +127,10 @@ pb200_status enable_kernel_smem() {
     return PB200_OK;
 }
 
+// coefficient window for the fast divisions (pb200_kernels.cuh: in_div_range)
 bool coef_in_div_range(double v) {
     const double a = std::fabs(v);
-    return a == 0.0 || (a >= 0x1p-400 && a <= 0x1p400);
+    return a == 0.0 || (a >= 0x1p-50 && a <= 0x1p300);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -242,7 +243,7 @@ pb200_status Solver::create(const pb200_params &params) {
     g.N = prm.N;
     c = make_consts(prm);
     // the coefficients are 1, 1/eps or a blend of the two (S4:167-177): div_const's fast path needs them in range
-    safe_div = !(coef_in_div_range(1.0 / c.eps) && coef_in_div_range(c.eps) && coef_in_div_range(c.f_val));
+    safe_div = !(coef_in_div_range(1.0 / c.eps) && c.h1 <= 0x1p10 && c.h2 <= 0x1p10);
     CK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     st = enable_kernel_smem();
     if (st != PB200_OK) return st;
@@ -348,7 +349,7 @@ void Solver::launch_iteration(long long k, bool first) {
     launch_k2(k2_args(k));
     if (c.multi) {
         exchange_r_halo();
-        allreduce(1, 3);
+        allreduce(1, 2);
         finalize_kernel<<<1, 1, 0, stream>>>(ctl, c, trace, 0);
     }
 }
@@ -424,7 +425,7 @@ pb200_status Solver::solve(pb200_result *res) {
             CK(cudaEventRecord(ev_poll[slot], stream));
             if (pending >= 0) { // look at the batch BEFORE the one just queued: the GPU never idles
                 CK(cudaEventSynchronize(ev_poll[pending]));
-                done = h_ctl[pending].done != 0 || h_ctl[pending].fault != 0;
+                done = h_ctl[pending].done != 0;
             }
             pending = slot;
             slot ^= 1;
@@ -452,16 +453,6 @@ pb200_status Solver::solve(pb200_result *res) {
     CK(cudaEventElapsedTime(&ms_call, ev_call0, ev_call1));
     const Ctl &hc = h_ctl[0];
     solved = true;
-    if (hc.fault && !safe_div) {
-        // A value left the range in which the fast divisions are proven exact (|x| outside 2^-400..2^400): the
-        // run is void. Repeat it with IEEE divides everywhere; this handle stays in that mode.
-        safe_div = true;
-        if (graph_exec) {
-            cudaGraphExecDestroy(graph_exec);
-            graph_exec = nullptr;
-        }
-        return solve(res);
-    }
     last_iter = hc.iter;
     if (res) {
         std::memset(res, 0, sizeof(*res));
@@ -483,6 +474,7 @@ pb200_status Solver::solve(pb200_result *res) {
         res->algo_gbps = res->pt_it_per_s * 104.0 * 1e-9;
         res->kernel_launches = launches - launches0;
         res->t_device_s = ms_call * 1e-3;
+        res->safe_mode = safe_div ? 1.0 : 0.0;
     }
     return PB200_OK;
 }

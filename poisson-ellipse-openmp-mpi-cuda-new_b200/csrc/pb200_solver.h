@@ -21,7 +21,7 @@ void choose_process_grid(int size, int &Px, int &Py);
 void decompose_2d(int M, int N, int Px, int Py, int rank, int &i0, int &i1, int &j0, int &j1);
 pb200_status validate(const pb200_params &p);
 Consts make_consts(const pb200_params &p);
-bool coef_in_div_range(double v); // zero, or 2^-400 <= |v| <= 2^400
+bool coef_in_div_range(double v); // zero, or 2^-50 <= |v| <= 2^300
 int pitch_for(int ny);
 int cpitch_for(int ny);
 pb200_status enable_kernel_smem();

@@ -203,6 +203,7 @@ def test_solve_matches_reference_and_oracle(oracle, golden, golden_arrays, key):
         w = s.solution()
         trace = s.trace(tl)
     assert res.iterations == golden["iters_stage3"][key]          # unmodified reference solve_mpi
+    assert res.safe_mode == 0.0
     assert res.stop_reason == pb.STOP_CONVERGED and res.first_converged_iter == res.iterations
     ores, ow, otrace = oracle.solve(m, n, want_w=True, trace_len=tl)
     assert res.iterations == ores.iterations
@@ -275,6 +276,36 @@ def test_fixed_iters_and_max_iter(oracle):
     assert res.iterations == 1
     res, _ = pb.run(pb.default_params(40, 40, max_iter=50))
     assert res.iterations == 50 and res.stop_reason == pb.STOP_CONVERGED
+
+
+def test_far_past_convergence(oracle):
+    """Run far past convergence with a fixed iteration budget: the loop must end where the reference's would, at the
+    |(Ap,p)| < 1e-15 guard (S4:876), with the oracle's result. (The underflow ring of the iterates -- values below
+    2^-840 and denormals, which need the IEEE-divide rows inside the kernels -- only appears on grids whose exterior
+    is hundreds of cells deep: test_long_solves_reference_iteration_counts covers it.)"""
+    m, n, it = 160, 240, 900
+    with pb.Solver(pb.default_params(m, n, fixed_iters=it, trace_len=it)) as s:
+        res = s.solve()
+        w = s.solution()
+        trace = s.trace(it)
+    ores, ow, otrace = oracle.solve(m, n, fixed_iters=it, want_w=True, trace_len=it)
+    assert res.safe_mode == 0.0
+    assert res.iterations == ores.iterations          # both stop early if the |denom| < 1e-15 guard fires (S4:876)
+    assert rel(res.w_norm_E, ores.w_norm_E) < RTOL_NORM
+    np.testing.assert_allclose(w, ow, rtol=0, atol=1e-11)
+    assert res.stop_reason == pb.STOP_DENOM and ores.denom_break == 1
+    np.testing.assert_allclose(trace[:300], otrace[:300], rtol=1e-8, atol=0)
+
+
+@pytest.mark.parametrize("m,n,want", [(1600, 2400, 1858), (2400, 3200, 2449)])
+def test_long_solves_reference_iteration_counts(m, n, want):
+    """The reference's published counts on its two largest grids, twice: any race in the kernels'
+    shared-memory pipeline shows up here as a run-to-run difference."""
+    a, _ = pb.run(pb.default_params(m, n))
+    b, _ = pb.run(pb.default_params(m, n))
+    assert a.iterations == b.iterations == want
+    assert (a.w_norm_E, a.diff_norm, a.zr) == (b.w_norm_E, b.diff_norm, b.zr)
+    assert a.safe_mode == 0.0
 
 
 def test_other_problem_parameters(oracle):
