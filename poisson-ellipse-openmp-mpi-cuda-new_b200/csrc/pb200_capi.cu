@@ -69,8 +69,7 @@ struct OpBlock {
         for (double *q : {f.a, f.b, f.D, f.w, f.r, f.p[0], f.p[1], Ap}) CK(cudaMemset(q, 0, f.elems * sizeof(double)));
         wn = (ny + K1_OWN - 1) / K1_OWN;
         // small pieces on purpose (3 rows per warp) so that the tests cross many piece and window boundaries
-        const long long T = (long long)wn * nx;
-        k1_grid = dim3(std::max((wn + K1_WARPS - 1) / K1_WARPS, (int)std::min<long long>(1024, (T + 3LL * K1_WARPS - 1) / (3LL * K1_WARPS))), 1, 1);
+        k1_grid = dim3(((nx + 2) / 3) * ((wn + K1_WARPS - 1) / K1_WARPS), 1, 1);
         k2_grid = k1_grid;
         init_grid = dim3((ny + INIT_THREADS - 1) / INIT_THREADS, std::min(nx, 1024), 1);
         size_t nb = (size_t)k1_grid.x * k1_grid.y;

@@ -168,11 +168,21 @@ __device__ __forceinline__ bool grid_reduce(double (&v)[NV], double *partials, u
     __syncthreads();
     if (!s_last) return false;
     __threadfence();
-    // last block: thread t sums partials t, t+THREADS, ... in order; then the fixed tree above.
+    // last block: thread t sums partials t, t+THREADS, ... in that order (loads issued eight at a time so that their
+    // latencies overlap; the additions keep the sequential order); then the fixed tree above.
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
+        const double *pk = partials + (size_t)k * nblocks;
         double s = 0.0;
-        for (unsigned i = threadIdx.x; i < nblocks; i += THREADS) s += __ldcg(&partials[(size_t)k * nblocks + i]);
+        unsigned i = threadIdx.x;
+        for (; i + 7u * THREADS < nblocks; i += 8u * THREADS) {
+            double v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = __ldcg(pk + i + u * THREADS);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) s += v[u];
+        }
+        for (; i < nblocks; i += THREADS) s += __ldcg(pk + i);
         double w = warp_sum(s);
         if (lane == 0) s_w[k][warp] = w;
     }
@@ -515,17 +525,30 @@ struct Lane {
 struct Part {
     int nsub;                  // 0 or 1 sub-segments (kept as a list: the kernels loop over it)
     int wcol[1], lo[1], hi[1]; // window and inclusive row range
+    int cta_rows;              // rows of the band this CTA works on (same for all its warps; 0 = none)
 };
 
-__device__ __forceinline__ Part make_part(int gw, int nw, int wn, int nx) {
+// CTA c takes CTA-window c % wcn (K1_WARPS adjacent warp windows) of band c / wcn, wcn = ceil(windows / K1_WARPS).
+__device__ __forceinline__ Part make_part(int cta, int warp, int ncta, int wn, int nx) {
     Part p;
-    const int nb = max(1, nw / wn);
-    const int b = gw / wn;
-    p.wcol[0] = gw - b * wn;
+    const int wcn = (wn + K1_WARPS - 1) / K1_WARPS;
+    const int nb = max(1, ncta / wcn);
+    const int b = cta / wcn;
+    p.wcol[0] = (cta - b * wcn) * K1_WARPS + warp;
     p.lo[0] = 1 + (int)(((long long)nx * b) / nb);
     p.hi[0] = (int)(((long long)nx * (b + 1)) / nb);
-    p.nsub = (b < nb && p.lo[0] <= p.hi[0]) ? 1 : 0;
+    p.cta_rows = (b < nb && p.lo[0] <= p.hi[0]) ? p.hi[0] - p.lo[0] + 1 : 0;
+    p.nsub = (p.cta_rows > 0 && p.wcol[0] < wn) ? 1 : 0;
     return p;
+}
+
+// Optional: keep the warps of a CTA on the same row (they then ask DRAM for adjacent 1 KB pieces of a row at the same
+// time). Every warp of the CTA, working or not, passes the same number of these barriers.
+#ifndef PB200_ROWSYNC
+#define PB200_ROWSYNC 0
+#endif
+__device__ __forceinline__ void row_sync(int r) {
+    if (PB200_ROWSYNC > 0 && (r % (PB200_ROWSYNC > 0 ? PB200_ROWSYNC : 1)) == 0) __syncthreads();
 }
 
 __device__ __forceinline__ Lane make_lane(const Geom &g, int lane, int warp, int wcol, int i_lo, int i_hi) {
@@ -697,7 +720,7 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
     const double h1 = A.c.h1, h2 = A.c.h2, rh1 = A.c.rh1, rh2 = A.c.rh2, mih1 = A.c.mih1, mih2 = A.c.mih2;
     const double inv_eps = A.c.inv_eps;
     const double beta = FIRST ? 0.0 : ctl->beta;
-    const Part part = make_part(blockIdx.x * K1_WARPS + warp_id, gridDim.x * K1_WARPS, A.wn, g.nx);
+    const Part part = make_part(blockIdx.x, warp_id, gridDim.x, A.wn, g.nx);
 
     double acc[1] = {0.0};
     unsigned tcount = 0u; // pipeline units consumed so far by this warp: stage and mbarrier parity follow from it
@@ -722,6 +745,9 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         const unsigned char *c_src = A.cls + cls_index(g.cpitch, 0, L.wcol, 0);
         auto issue = [&](int t) {
             if (L.lane == 0 && t < nunits) {
+#ifdef PB200_FENCE_LANE0
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
                 const int st = (int)((tcount + (unsigned)t) & (STAGES - 1));
                 const size_t n = (size_t)(row0 + t);
                 const unsigned bar = bar_s + 8u * st, dst = ring_s + (unsigned)(st * K1_STAGE_BYTES);
@@ -744,7 +770,9 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
             // the proxy fence it may overtake the generic-proxy reads above (observed: wrong, run-to-run varying
             // results on long solves).
             __syncwarp();
+#ifndef PB200_FENCE_LANE0
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
             issue(t + STAGES);
             return in;
         };
@@ -802,10 +830,16 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
 
         const unsigned last = (L.i_hi == g.nx) ? L.pw : 0u; // row i_hi+1 belongs to the next segment unless it is ring row nx+1
 #pragma unroll 1
-        for (int i = L.i_lo; i < L.i_hi; ++i) row_step(i, fetch(i - L.i_lo + 2), L.pw);
+        for (int i = L.i_lo; i < L.i_hi; ++i) {
+            row_sync(i - L.i_lo);
+            row_step(i, fetch(i - L.i_lo + 2), L.pw);
+        }
+        row_sync(L.i_hi - L.i_lo);
         row_step(L.i_hi, fetch(L.i_hi - L.i_lo + 2), last);
         tcount += (unsigned)nunits;
     }
+    if (part.nsub == 0)
+        for (int r = 0; r < part.cta_rows; ++r) row_sync(r); // a warp without a window still meets its CTA's barriers
 
     double tot[1];
     if (grid_reduce<1, K1_THREADS>(acc, A.partials, &ctl->ticket[0], tot)) {
@@ -877,7 +911,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
     const double h1 = A.c.h1, h2 = A.c.h2, rh1 = A.c.rh1, rh2 = A.c.rh2, mih1 = A.c.mih1, mih2 = A.c.mih2;
     const double inv_eps = A.c.inv_eps;
 
-    const Part part = make_part(blockIdx.x * K1_WARPS + warp_id, gridDim.x * K1_WARPS, A.wn, g.nx);
+    const Part part = make_part(blockIdx.x, warp_id, gridDim.x, A.wn, g.nx);
 
     double acc[2] = {0.0, 0.0};
     unsigned tcount = 0u;
@@ -901,6 +935,9 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         const unsigned char *c_src = A.cls + cls_index(g.cpitch, 0, L.wcol, 0);
         auto issue = [&](int t) {
             if (L.lane == 0 && t < nunits) {
+#ifdef PB200_FENCE_LANE0
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
                 const int st = (int)((tcount + (unsigned)t) & (STAGES - 1));
                 const size_t i = (size_t)(L.i_lo + t);
                 const unsigned bar = bar_s + 8u * st, dst = ring_s + (unsigned)(st * K2_STAGE_BYTES);
@@ -922,7 +959,9 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
             in.r = lds4(base + 2 * ROW_BYTES, L.lane);
             in.cls = *reinterpret_cast<const unsigned *>(base + 3 * ROW_BYTES + 4 * L.lane);
             __syncwarp(); // see k1_kernel: reads first, proxy fence, then the refill
+#ifndef PB200_FENCE_LANE0
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
             issue(t + STAGES);
             return in;
         };
@@ -977,9 +1016,14 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         };
 
 #pragma unroll 1
-        for (int i = L.i_lo; i <= L.i_hi; ++i) row_step(i, fetch(i - L.i_lo));
+        for (int i = L.i_lo; i <= L.i_hi; ++i) {
+            row_sync(i - L.i_lo);
+            row_step(i, fetch(i - L.i_lo));
+        }
         tcount += (unsigned)nunits;
     }
+    if (part.nsub == 0)
+        for (int r = 0; r < part.cta_rows; ++r) row_sync(r);
 
     double tot[2];
     if (grid_reduce<2, K2_THREADS>(acc, A.partials, &ctl->ticket[1], tot)) {

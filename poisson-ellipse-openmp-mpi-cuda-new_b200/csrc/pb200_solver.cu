@@ -186,20 +186,37 @@ Solver::~Solver() {
 }
 
 // Grid of a marching kernel: the rows are cut into bands of `rows` rows and every warp takes one 124-column window of
-// one band (make_part). Measured on a B200 at 8192^2: throughput rises with the number of pieces up to about 8 waves
-// (bands of ~20 rows: 45 -> 73 G pt*it/s from 1 to 8+ waves) and is flat beyond; small grids get shorter bands (down
-// to 4 rows) so that every SM has work.
+// one band (make_part). The band height is chosen with a small cost model fitted to B200 measurements at 8192^2:
+//   * a piece costs rows + 2 row steps (two extra rows start every piece);
+//   * the kernel lasts ceil(blocks / resident blocks) waves;
+//   * per-warp speed grows with the number of waves in flight behind each other (46 / 60 / 64.5 / 67 / 71 / 72.5
+//     G pt*it/s at 1 / 2 / 3 / 4 / 6 / 8 waves) -- many short pieces beat one resident wave.
+// PB200_ROWS overrides the choice (tuning).
+static double wave_gain(double w) {
+    static const double x[] = {0.0, 0.5, 1.0, 2.0, 3.0, 4.0, 6.0, 8.0}, y[] = {0.0, 0.42, 0.63, 0.83, 0.89, 0.925, 0.98, 1.0};
+    if (w >= 8.0) return 1.0;
+    for (int i = 1; i < 8; ++i)
+        if (w <= x[i]) return y[i - 1] + (y[i] - y[i - 1]) * (w - x[i - 1]) / (x[i] - x[i - 1]);
+    return 1.0;
+}
+
 int march_blocks(int resident_blocks, int wn, int nx) {
-    int rows = 20;
-    if (const char *e = std::getenv("PB200_ROWS")) rows = std::max(1, atoi(e)); // tuning knob
-    else {
-        const long long T = static_cast<long long>(wn) * nx;
-        const long long per_warp = T / std::max(1LL, static_cast<long long>(resident_blocks) * K1_WARPS);
-        rows = static_cast<int>(std::min<long long>(20, std::max<long long>(4, per_warp)));
+    auto blocks_for = [&](int rows) { // bands x CTA-windows (make_part)
+        return ((nx + rows - 1) / rows) * ((wn + K1_WARPS - 1) / K1_WARPS);
+    };
+    if (const char *e = std::getenv("PB200_ROWS")) return blocks_for(std::max(1, atoi(e)));
+    const double resident = std::max(1, resident_blocks);
+    int best_rows = 20;
+    double best_cost = 1e300;
+    for (int rows = 4; rows <= 24; ++rows) {
+        const double waves = blocks_for(rows) / resident;
+        const double cost = std::ceil(waves) * (rows + 2) / wave_gain(waves);
+        if (cost < best_cost * 0.999) {
+            best_cost = cost;
+            best_rows = rows;
+        }
     }
-    const int nb = (nx + rows - 1) / rows;
-    const long long warps = static_cast<long long>(nb) * wn;
-    return static_cast<int>((warps + K1_WARPS - 1) / K1_WARPS);
+    return blocks_for(best_rows);
 }
 
 void Solver::plan_launch() {
