@@ -1050,6 +1050,7 @@ __global__ void finalize_kernel(Ctl *ctl, Consts c, double *trace, int init) {
 // norms of the result (reporting only): sum w^2, sum r^2, max |w| over the interior.
 __global__ void __launch_bounds__(256) norms_kernel(Geom g, const double *__restrict__ w, const double *__restrict__ r,
                                                     double *partials, unsigned int *ticket, double *out3) {
+    __shared__ double s_max[8];
     double acc[2] = {0.0, 0.0};
     double mx = 0.0;
     const int lj = 1 + blockIdx.x * blockDim.x + threadIdx.x;
@@ -1061,13 +1062,39 @@ __global__ void __launch_bounds__(256) norms_kernel(Geom g, const double *__rest
             acc[1] += vr * vr;
             mx = fmax(mx, fabs(vw));
         }
-    // max via ordered-int atomics on the bit pattern (non-negative doubles order like integers)
-    atomicMax(reinterpret_cast<unsigned long long *>(&out3[2]), (unsigned long long)__double_as_longlong(mx));
+    // block maximum, then ONE atomic per block (bit pattern of a non-negative double orders like an integer)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_down_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < 8; ++k) mx = fmax(mx, s_max[k]);
+        atomicMax(reinterpret_cast<unsigned long long *>(&out3[2]), (unsigned long long)__double_as_longlong(mx));
+    }
     double tot[2];
     if (grid_reduce<2, 256>(acc, partials, ticket, tot)) {
         out3[0] = tot[0];
         out3[1] = tot[1];
     }
+}
+
+// Back to the initial state of a solve without recomputing the coefficients: w = p = 0, r = B (S4:805, 813, 182-191).
+__global__ void __launch_bounds__(256) reset_kernel(Geom g, Consts c, double *__restrict__ r, double *__restrict__ w,
+                                                    double *__restrict__ p0, double *__restrict__ p1) {
+    const int lj = blockIdx.x * blockDim.x + threadIdx.x;
+    const int li = blockIdx.y;
+    if (lj >= g.pitch) return;
+    const size_t o = (size_t)li * g.pitch + lj;
+    double vr = 0.0;
+    const int gi = g.gi0 + li, gj = g.gj0 + lj;
+    if (lj <= g.ny + 1 && gi >= 1 && gi <= g.M - 1 && gj >= 1 && gj <= g.N - 1) {
+        const double x = c.A1 + gi * c.h1, y = c.A2 + gj * c.h2;
+        vr = (x * x + c.ell_c * y * y < 1.0) ? c.f_val : 0.0; // S4:32-34, 189
+    }
+    r[o] = vr;
+    w[o] = 0.0;
+    p0[o] = 0.0;
+    p1[o] = 0.0;
 }
 
 // Generic weighted inner product (operator entry point; the solver's dots are fused into K1/K2).

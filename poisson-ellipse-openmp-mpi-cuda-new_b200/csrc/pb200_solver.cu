@@ -292,7 +292,9 @@ pb200_status Solver::create(const pb200_params &params) {
 
 pb200_status Solver::run_setup() {
     dim3 grid((f.g.pitch + 255) / 256, f.g.nx + 2);
-    setup_kernel<<<grid, 256, 0, stream>>>(f.g, c, f.a, f.b, f.D, f.r, f.w, f.p[0], f.p[1], nullptr, f.cls);
+    if (coefficients_ready) reset_kernel<<<grid, 256, 0, stream>>>(f.g, c, f.r, f.w, f.p[0], f.p[1]); // a, b, D, classes stay
+    else setup_kernel<<<grid, 256, 0, stream>>>(f.g, c, f.a, f.b, f.D, f.r, f.w, f.p[0], f.p[1], nullptr, f.cls);
+    coefficients_ready = true;
     ++launches;
     CK(cudaGetLastError());
     return PB200_OK;

@@ -62,6 +62,7 @@ struct Solver {
     long long last_iter = 0;
     double t_setup = 0.0;
     bool solved = false;
+    bool coefficients_ready = false;
     Comm *comm = nullptr;
 
     ~Solver();
