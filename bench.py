@@ -174,6 +174,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--iters", type=int, default=ITERS)
     ap.add_argument("--block", type=int, default=BLOCK, help="cells per GPU per side (default: the named workload)")
+    ap.add_argument("--grid", type=int, nargs=2, metavar=("M", "N"),
+                    help="a fixed M x N grid split over the GPUs (strong scaling, e.g. BASELINE configs[2]: 2400 3200) "
+                         "instead of the named weak-scaling workload")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -201,6 +204,8 @@ def main():
 
     BLOCK = args.block
     M, N, px, py = workload(world, pb)
+    if args.grid:
+        M, N = args.grid
     pts = (M - 1) * (N - 1)
     prm = pb.default_params(M, N, fixed_iters=args.iters, device=local_rank, nranks=world, rank=rank, Px=px, Py=py)
     solver = pb.Solver(prm)
@@ -320,8 +325,8 @@ def main():
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True,
-                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": f"{M}x{N} fp64 grid ({px}x{py} blocks of {BLOCK}x{BLOCK} cells, one per GPU), "
+                "scaling": "strong" if args.grid else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": f"{M}x{N} fp64 grid ({px}x{py} blocks of {M // px}x{N // py} cells, one per GPU), "
                                        f"fused PCG iteration, fixed {args.iters} iterations per step",
                            "grid": [M, N], "process_grid": [px, py], "iterations_per_step": args.iters,
                            "l2": "inputs larger than L2 (each iteration streams ~7 GB per GPU)",

@@ -109,10 +109,6 @@ struct OpBlock {
                         g.ny * sizeof(double), g.nx, cudaMemcpyDeviceToHost));
         return PB200_OK;
     }
-    pb200_status faulted(bool *f) { // kept for the call sites: out-of-window rows are handled inside the kernels
-        *f = false;
-        return PB200_OK;
-    }
     pb200_status set_ctl(double beta, double zr_old) {
         Ctl h{};
         h.beta = beta;
@@ -341,11 +337,11 @@ pb200_status pb200_op_setup(const pb200_params *p, int32_t i0, int32_t i1, int32
     return PB200_OK;
 }
 
-static pb200_status op_apply_A_impl(const pb200_params *p, const double *pvec, const double *a, const double *b, double *Ap,
-                                    int32_t nx, int32_t ny, bool safe, bool *fault) {
+pb200_status pb200_op_apply_A(const pb200_params *p, const double *pvec, const double *a, const double *b, double *Ap,
+                              int32_t nx, int32_t ny) {
+    if (!p || !pvec || !a || !b || !Ap) { set_error("null argument"); return PB200_ERR_INVALID; }
     OpBlock ob;
     TRY(ob.init(*p, nx, ny));
-    ob.safe_div = safe;
     TRY(ob.put(ob.f.p[0], pvec));
     TRY(ob.put(ob.f.a, a));
     TRY(ob.put(ob.f.b, b));
@@ -356,25 +352,15 @@ static pb200_status op_apply_A_impl(const pb200_params *p, const double *pvec, c
     TRY(ob.set_ctl(1.0, 0.0));
     TRY(ob.k1(false, ob.f.p[0], ob.f.p[1]));
     CK(cudaDeviceSynchronize());
-    TRY(ob.faulted(fault));
-    if (!*fault) TRY(ob.get_interior(Ap, ob.Ap));
+    TRY(ob.get_interior(Ap, ob.Ap));
     return PB200_OK;
 }
 
-pb200_status pb200_op_apply_A(const pb200_params *p, const double *pvec, const double *a, const double *b, double *Ap,
-                              int32_t nx, int32_t ny) {
-    if (!p || !pvec || !a || !b || !Ap) { set_error("null argument"); return PB200_ERR_INVALID; }
-    bool fault = false;
-    TRY(op_apply_A_impl(p, pvec, a, b, Ap, nx, ny, false, &fault));
-    if (fault) TRY(op_apply_A_impl(p, pvec, a, b, Ap, nx, ny, true, &fault)); // out of the fast divisions' range: IEEE divides
-    return PB200_OK;
-}
-
-static pb200_status op_apply_Dinv_impl(const pb200_params *p, const double *r, const double *a, const double *b, double *z,
-                                       int32_t nx, int32_t ny, bool safe, bool *fault) {
+pb200_status pb200_op_apply_Dinv(const pb200_params *p, const double *r, const double *a, const double *b, double *z,
+                                 int32_t nx, int32_t ny) {
+    if (!p || !r || !a || !b || !z) { set_error("null argument"); return PB200_ERR_INVALID; }
     OpBlock ob;
     TRY(ob.init(*p, nx, ny));
-    ob.safe_div = safe;
     TRY(ob.put(ob.f.r, r));
     TRY(ob.put(ob.f.a, a));
     TRY(ob.put(ob.f.b, b));
@@ -384,26 +370,16 @@ static pb200_status op_apply_Dinv_impl(const pb200_params *p, const double *r, c
     TRY(ob.set_ctl(0.0, 0.0));
     TRY(ob.k1(true, ob.f.p[0], ob.f.p[1])); // iteration-1 form of K1: p' = D^-1 r
     CK(cudaDeviceSynchronize());
-    TRY(ob.faulted(fault));
-    if (!*fault) TRY(ob.get_interior(z, ob.f.p[1]));
+    TRY(ob.get_interior(z, ob.f.p[1]));
     return PB200_OK;
 }
 
-pb200_status pb200_op_apply_Dinv(const pb200_params *p, const double *r, const double *a, const double *b, double *z,
-                                 int32_t nx, int32_t ny) {
-    if (!p || !r || !a || !b || !z) { set_error("null argument"); return PB200_ERR_INVALID; }
-    bool fault = false;
-    TRY(op_apply_Dinv_impl(p, r, a, b, z, nx, ny, false, &fault));
-    if (fault) TRY(op_apply_Dinv_impl(p, r, a, b, z, nx, ny, true, &fault));
-    return PB200_OK;
-}
-
-static pb200_status op_iteration_impl(const pb200_params *p, double *w, double *r, double *pvec, double *Ap, const double *a,
-                                      const double *b, int32_t nx, int32_t ny, double beta, double zr_old, int32_t first,
-                                      double out[4], bool safe, bool *fault) {
+pb200_status pb200_op_iteration(const pb200_params *p, double *w, double *r, double *pvec, double *Ap, const double *a,
+                                const double *b, int32_t nx, int32_t ny, double beta, double zr_old, int32_t first,
+                                double out[4]) {
+    if (!p || !w || !r || !pvec || !a || !b || !out) { set_error("null argument"); return PB200_ERR_INVALID; }
     OpBlock ob;
     TRY(ob.init(*p, nx, ny));
-    ob.safe_div = safe;
     TRY(ob.put(ob.f.w, w));
     TRY(ob.put(ob.f.r, r));
     TRY(ob.put(ob.f.p[0], pvec));
@@ -418,7 +394,6 @@ static pb200_status op_iteration_impl(const pb200_params *p, double *w, double *
     CK(cudaDeviceSynchronize());
     Ctl h{};
     CK(cudaMemcpy(&h, ob.ctl, sizeof(Ctl), cudaMemcpyDeviceToHost));
-    *fault = false;
     out[0] = h.denom;
     out[1] = h.alpha;
     out[2] = h.red[1];
@@ -427,16 +402,6 @@ static pb200_status op_iteration_impl(const pb200_params *p, double *w, double *
     TRY(ob.get_interior(r, ob.f.r));
     TRY(ob.get_interior(pvec, ob.f.p[1]));
     if (Ap) TRY(ob.get_interior(Ap, ob.Ap));
-    return PB200_OK;
-}
-
-pb200_status pb200_op_iteration(const pb200_params *p, double *w, double *r, double *pvec, double *Ap, const double *a,
-                                const double *b, int32_t nx, int32_t ny, double beta, double zr_old, int32_t first,
-                                double out[4]) {
-    if (!p || !w || !r || !pvec || !a || !b || !out) { set_error("null argument"); return PB200_ERR_INVALID; }
-    bool fault = false;
-    TRY(op_iteration_impl(p, w, r, pvec, Ap, a, b, nx, ny, beta, zr_old, first, out, false, &fault));
-    if (fault) TRY(op_iteration_impl(p, w, r, pvec, Ap, a, b, nx, ny, beta, zr_old, first, out, true, &fault));
     return PB200_OK;
 }
 
