@@ -134,8 +134,10 @@ def run_reference(args, rank, world):
     sample = (f"{M}x{N} grid (one GPU's block of the workload), solve_mpi with max_iter={REF_ITERS} per step, "
               f"coefficient setup included as in the reference's own timings; 1 rank x {cores} OpenMP threads")
     line.update({"value": value, "ms_per_step": dt / args.steps * 1e3,
-                 "config": {"workload": f"{M}x{N} fp64 grid, reference stage3 hybrid (hybrid.cpp) on host cores",
-                            "iterations_per_step": REF_ITERS},
+                 "config": {"workload": f"{M}x{N} fp64 grid (1x1 blocks of {M}x{N} cells, one per GPU), PCG iteration, "
+                                        f"fixed {REF_ITERS} iterations per step (bounded sample of the 100-iteration step)",
+                            "grid": [M, N], "process_grid": [1, 1], "iterations_per_step": REF_ITERS,
+                            "implementation": "reference stage3 hybrid (hybrid.cpp, unmodified) on the host cores"},
                  "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
                  "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                  "gpu_launches": 0})
@@ -296,8 +298,9 @@ def main():
         assert float(w_host.abs().max()) > 0
         e2e = {"value": pts * args.iters / t_e2e, "unit": UNIT, "h2d_bytes_per_step": ctypes.sizeof(prm1),
                "d2h_bytes_per_step": (M - 1) * (N - 1) * 8, "ms_per_call": t_e2e * 1e3,
-               "call": "pb200_run(params, result, w_host, ld): cudaMalloc + coefficient kernel + iterations + solution D2H + cudaFree"}
+               "call": "pb200_run(params, result, w_host, ld) with HOST buffers: reset of the workspace the call keeps from an identical earlier call, iterations, solution D2H into pinned memory (first call: + cudaMalloc + coefficient kernel, ms_first_call)", "ms_first_call": times[0] * 1e3}
         del w_host
+        pb.release_cache()
     else:
         # multi-GPU: create + attach + solve + solution D2H per rank, wall clock, max over ranks
         uid2 = fresh_uid()

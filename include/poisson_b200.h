@@ -136,8 +136,11 @@ pb200_status pb200_profile_iteration(pb200_solver *s, int32_t iters, double ms_o
 void pb200_destroy(pb200_solver *s);
 
 /* One call = the reference binary's whole solver phase: create + solve (+ solution to host when
- * w_host != NULL, ld as above) + destroy. Single rank. */
+ * w_host != NULL, ld as above). Single rank. The handle is kept (one per host thread) so that an identical
+ * next call reuses the device workspace and the coefficients instead of allocating and recomputing them;
+ * any other call replaces it, pb200_release_cache() or the end of the thread frees it. */
 pb200_status pb200_run(const pb200_params *p, pb200_result *res, double *w_host, int64_t ld);
+void pb200_release_cache(void);
 
 /* ---- operator-level entry points (parity tests; same kernels as the solver) ------------- */
 /* All arrays are HOST pointers in the reference's layout: (nx+2)*(ny+2) doubles, idx = li*(ny+2)+lj

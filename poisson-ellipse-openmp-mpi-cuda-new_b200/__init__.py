@@ -56,7 +56,7 @@ class PB200Error(RuntimeError):
 EXPORTS = ["pb200_api_version", "pb200_status_string", "pb200_last_error", "pb200_device_count",
            "pb200_default_params", "pb200_choose_process_grid", "pb200_decompose_2d", "pb200_create",
            "pb200_comm_unique_id", "pb200_attach_comm", "pb200_solve", "pb200_get_solution", "pb200_get_trace",
-           "pb200_get_field", "pb200_profile_iteration", "pb200_destroy", "pb200_run", "pb200_op_setup", "pb200_op_apply_A",
+           "pb200_get_field", "pb200_profile_iteration", "pb200_destroy", "pb200_run", "pb200_release_cache", "pb200_op_setup", "pb200_op_apply_A",
            "pb200_op_apply_Dinv", "pb200_op_iteration", "pb200_op_dot", "pb200_dot_noalloc", "pb200_selftest_div"]
 
 _lib = None
@@ -88,6 +88,7 @@ def lib():
         L.pb200_destroy.argtypes = [C.c_void_p]
         L.pb200_destroy.restype = None
         L.pb200_run.argtypes = [C.POINTER(Params), C.POINTER(Result), c_double_p, C.c_int64]
+        L.pb200_release_cache.restype = None
         L.pb200_op_setup.argtypes = [C.POINTER(Params)] + [C.c_int32] * 4 + [c_double_p] * 4
         L.pb200_op_apply_A.argtypes = [C.POINTER(Params)] + [c_double_p] * 4 + [C.c_int32] * 2
         L.pb200_op_apply_Dinv.argtypes = [C.POINTER(Params)] + [c_double_p] * 4 + [C.c_int32] * 2
@@ -214,6 +215,11 @@ def run(params, want_w=False):
     w = np.zeros((params.M + 1, params.N + 1)) if want_w else None
     _check(lib().pb200_run(C.byref(params), C.byref(res), _ptr(w), params.N + 1))
     return res, w
+
+
+def release_cache():
+    """Free the device workspace pb200_run keeps for an identical next call."""
+    lib().pb200_release_cache()
 
 
 def op_setup(params, block=None):

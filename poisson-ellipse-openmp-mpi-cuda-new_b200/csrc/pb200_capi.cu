@@ -4,6 +4,7 @@
 #include "pb200_solver.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <new>
@@ -307,14 +308,40 @@ pb200_status pb200_profile_iteration(pb200_solver *s, int32_t iters, double ms_o
 
 void pb200_destroy(pb200_solver *s) { delete s; }
 
+// pb200_run keeps the handle of its last call (per host thread): an identical call then skips the device allocation
+// and the coefficient kernel, which at 8192^2 cost about as much as 15 iterations.
+namespace {
+struct RunCache {
+    std::unique_ptr<pb200_solver> solver;
+    pb200_params params{};
+};
+thread_local RunCache g_run_cache;
+} // namespace
+
+void pb200_release_cache(void) { g_run_cache.solver.reset(); }
+
 pb200_status pb200_run(const pb200_params *p, pb200_result *res, double *w_host, int64_t ld) {
     if (!p) { set_error("null argument"); return PB200_ERR_INVALID; }
     if (p->nranks != 1) { set_error("pb200_run is single-rank; use create/attach_comm/solve"); return PB200_ERR_INVALID; }
-    pb200_solver *s = nullptr;
-    TRY(pb200_create(p, &s));
-    std::unique_ptr<pb200_solver> guard(s);
-    TRY(s->impl.solve(res));
-    if (w_host) TRY(s->impl.get_solution(w_host, ld));
+    RunCache &rc = g_run_cache;
+    const bool reuse = rc.solver && std::memcmp(&rc.params, p, sizeof(*p)) == 0 && !std::getenv("PB200_NO_CACHE");
+    double t_setup = 0.0;
+    if (!reuse) {
+        rc.solver.reset(); // free the previous workspace before allocating the next
+        pb200_solver *s = nullptr;
+        TRY(pb200_create(p, &s));
+        rc.solver.reset(s);
+        rc.params = *p;
+        t_setup = s->impl.t_setup;
+    }
+    Solver &S = rc.solver->impl;
+    pb200_status st = S.solve(res);
+    if (st == PB200_OK && w_host) st = S.get_solution(w_host, ld);
+    if (st != PB200_OK) {
+        rc.solver.reset();
+        return st;
+    }
+    if (res) res->t_setup_s = t_setup; // 0 when the cached workspace was reused
     return PB200_OK;
 }
 
