@@ -179,6 +179,8 @@ def main():
     ap.add_argument("--grid", type=int, nargs=2, metavar=("M", "N"),
                     help="a fixed M x N grid split over the GPUs (strong scaling, e.g. BASELINE configs[2]: 2400 3200) "
                          "instead of the named weak-scaling workload")
+    ap.add_argument("--comm", default="peer", choices=["peer", "nccl"],
+                    help="multi-GPU exchange: peer = NVLink stores inside the kernels (default), nccl = NCCL calls per iteration")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -219,8 +221,17 @@ def main():
         dist.broadcast(uid, 0)
         return uid.cpu().numpy().tobytes()
 
+    def attach(s):
+        """NCCL communicator (start-up barrier, final norms), then peer-memory mode unless --comm nccl."""
+        s.attach_comm(fresh_uid())
+        if args.comm == "peer":
+            mine = torch.frombuffer(bytearray(s.peer_export()), dtype=torch.uint8).cuda()
+            every = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(every, mine)
+            s.peer_attach([bytes(t.cpu().numpy().tobytes()) for t in every])
+
     if world > 1:
-        solver.attach_comm(fresh_uid())
+        attach(solver)
 
     def barrier():
         if dist:
@@ -303,12 +314,11 @@ def main():
         pb.release_cache()
     else:
         # multi-GPU: create + attach + solve + solution D2H per rank, wall clock, max over ranks
-        uid2 = fresh_uid()
         barrier()
         t0 = time.perf_counter()
         s2 = pb.Solver(prm)
         t_c0 = time.perf_counter()
-        s2.attach_comm(uid2)            # NCCL communicator bootstrap (~1.5 s, once per job): not part of the step
+        attach(s2)                      # communicator bootstrap (~1.5 s, once per job): not part of the step
         t_comm = time.perf_counter() - t_c0
         r2 = s2.solve()
         i0, i1, j0, j1 = pb.decompose_2d(M, N, px, py, rank)
@@ -333,6 +343,7 @@ def main():
                                        f"fused PCG iteration, fixed {args.iters} iterations per step",
                            "grid": [M, N], "process_grid": [px, py], "iterations_per_step": args.iters,
                            "l2": "inputs larger than L2 (each iteration streams ~7 GB per GPU)",
+                           "comm": ("none" if world == 1 else args.comm),
                            "timing": "CUDA events on the solver stream inside pb200_solve, summed over steps, max over ranks"},
                 "algo_gbs": value * ALGO_BYTES * 1e-9, "algo_gbs_per_gpu": value * ALGO_BYTES * 1e-9 / world,
                 "wall_ms_per_step": wall_s / args.steps * 1e3,

@@ -41,7 +41,8 @@ enum {
 enum {
     PB200_STOP_MAX_ITER = 0,  /* ran max_iter (or fixed_iters) iterations (S4:847) */
     PB200_STOP_CONVERGED = 1, /* ||w(k+1)-w(k)|| < delta (S4:899-906) */
-    PB200_STOP_DENOM = 2      /* (Ap,p) guard fired (S4:876) */
+    PB200_STOP_DENOM = 2,     /* (Ap,p) guard fired (S4:876) */
+    PB200_STOP_COMM_TIMEOUT = 3 /* peer-memory mode: a rank did not answer in time (pb200_solve returns PB200_ERR_COMM) */
 };
 
 /*
@@ -118,6 +119,14 @@ pb200_status pb200_create(const pb200_params *p, pb200_solver **out);
  * (replaces MPI_Init/Comm_rank/Comm_size, S4:987-991). Collective over all ranks. */
 pb200_status pb200_comm_unique_id(uint8_t id_out[128]);
 pb200_status pb200_attach_comm(pb200_solver *s, const uint8_t unique_id[128]);
+/* Optional, after pb200_attach_comm: peer-memory mode. Each rank exports 256 bytes (where its mailbox and its residual
+ * array live), the host gathers the exports of all ranks in rank order (replaces nothing in the reference: it would be
+ * an MPI_Allgather there) and every rank attaches them. From then on the two iteration kernels exchange halos and
+ * partial sums themselves through NVLink stores into peer memory (CUDA IPC between processes, peer access between
+ * threads) -- no NCCL call inside the loop, and the loop is replayed as a CUDA graph. Up to 8 ranks on one node.
+ * Replaces exchange_halos_2d_gpu (S4:331-500) and the three MPI_Allreduce per iteration (S4:872, 893, 926). */
+pb200_status pb200_peer_export(pb200_solver *s, uint8_t blob_out[256]);
+pb200_status pb200_peer_attach(pb200_solver *s, const uint8_t *blobs_in_rank_order, int32_t nranks);
 /* Init (S4:803-843) + PCG loop (S4:845-943). Collective when nranks > 1. */
 pb200_status pb200_solve(pb200_solver *s, pb200_result *res);
 /* Copies this rank's block of w into a host array laid out as the WHOLE grid, (M+1) rows of

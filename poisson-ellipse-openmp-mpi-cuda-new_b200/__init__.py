@@ -17,7 +17,7 @@ LIB_PATH = os.environ.get("PB200_LIB") or os.path.join(HERE, "libpoisson_b200.so
 CLI_PATH = os.path.join(HERE, "poisson_b200")
 
 NORM_WEIGHTED, NORM_STAGE0 = 0, 1
-STOP_MAX_ITER, STOP_CONVERGED, STOP_DENOM = 0, 1, 2
+STOP_MAX_ITER, STOP_CONVERGED, STOP_DENOM, STOP_COMM_TIMEOUT = 0, 1, 2, 3
 
 c_double_p = C.POINTER(C.c_double)
 
@@ -55,7 +55,7 @@ class PB200Error(RuntimeError):
 # every symbol include/poisson_b200.h declares
 EXPORTS = ["pb200_api_version", "pb200_status_string", "pb200_last_error", "pb200_device_count",
            "pb200_default_params", "pb200_choose_process_grid", "pb200_decompose_2d", "pb200_create",
-           "pb200_comm_unique_id", "pb200_attach_comm", "pb200_solve", "pb200_get_solution", "pb200_get_trace",
+           "pb200_comm_unique_id", "pb200_attach_comm", "pb200_peer_export", "pb200_peer_attach", "pb200_solve", "pb200_get_solution", "pb200_get_trace",
            "pb200_get_field", "pb200_profile_iteration", "pb200_destroy", "pb200_run", "pb200_release_cache", "pb200_op_setup", "pb200_op_apply_A",
            "pb200_op_apply_Dinv", "pb200_op_iteration", "pb200_op_dot", "pb200_dot_noalloc", "pb200_selftest_div"]
 
@@ -79,6 +79,8 @@ def lib():
         L.pb200_create.argtypes = [C.POINTER(Params), C.POINTER(C.c_void_p)]
         L.pb200_comm_unique_id.argtypes = [C.c_char_p]
         L.pb200_attach_comm.argtypes = [C.c_void_p, C.c_char_p]
+        L.pb200_peer_export.argtypes = [C.c_void_p, C.c_char_p]
+        L.pb200_peer_attach.argtypes = [C.c_void_p, C.c_char_p, C.c_int32]
         L.pb200_solve.argtypes = [C.c_void_p, C.POINTER(Result)]
         L.pb200_get_solution.argtypes = [C.c_void_p, c_double_p, C.c_int64]
         L.pb200_get_trace.argtypes = [C.c_void_p, c_double_p, C.c_int32, C.POINTER(C.c_int32)]
@@ -160,6 +162,16 @@ class Solver:
 
     def attach_comm(self, unique_id):
         _check(lib().pb200_attach_comm(self.h, unique_id))
+
+    def peer_export(self):
+        """256-byte description of this rank's mailbox / residual array for peer-memory mode."""
+        buf = C.create_string_buffer(256)
+        _check(lib().pb200_peer_export(self.h, buf))
+        return buf.raw
+
+    def peer_attach(self, blobs):
+        """blobs: the exports of all ranks, in rank order."""
+        _check(lib().pb200_peer_attach(self.h, b"".join(blobs), len(blobs)))
 
     def solve(self):
         res = Result()

@@ -271,6 +271,16 @@ pb200_status pb200_attach_comm(pb200_solver *s, const uint8_t unique_id[128]) {
     return s->impl.attach_comm(unique_id);
 }
 
+pb200_status pb200_peer_export(pb200_solver *s, uint8_t blob_out[256]) {
+    if (!s || !blob_out) { set_error("null argument"); return PB200_ERR_INVALID; }
+    return s->impl.peer_export(blob_out);
+}
+
+pb200_status pb200_peer_attach(pb200_solver *s, const uint8_t *blobs, int32_t nranks) {
+    if (!s || !blobs) { set_error("null argument"); return PB200_ERR_INVALID; }
+    return s->impl.peer_attach(blobs, nranks);
+}
+
 pb200_status pb200_solve(pb200_solver *s, pb200_result *res) {
     if (!s) { set_error("null solver"); return PB200_ERR_INVALID; }
     return s->impl.solve(res);

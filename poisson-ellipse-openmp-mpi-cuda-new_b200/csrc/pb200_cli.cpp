@@ -17,6 +17,7 @@
 #include <iomanip>
 #include <iostream>
 #include <string>
+#include <atomic>
 #include <thread>
 #include <vector>
 
@@ -28,7 +29,7 @@ static void usage() {
     std::cerr <<
         "usage: poisson_b200 [M N] [--delta D] [--max-iter K] [--eps E] [--ellipse-k K] [--rect A1 B1 A2 B2] [--f F]\n"
         "                    [--norm weighted|stage0] [--gpus P] [--grid PXxPY] [--device D] [--fixed-iters K]\n"
-        "                    [--trace K] [--check-every K] [--no-graph] [--dump FILE(.npy|.txt|raw)] [--json FILE|-]\n"
+        "                    [--trace K] [--check-every K] [--no-graph] [--comm peer|nccl] [--dump FILE(.npy|.txt|raw)] [--json FILE|-]\n"
         "Solves -div(k grad u) = f on the rectangle with the ellipse x^2+(k y)^2<1 as fictitious domain (PCG).\n"
         "With no flags it behaves as the reference: `poisson_b200 M N`.\n";
 }
@@ -67,6 +68,7 @@ int main(int argc, char **argv) {
     pb200_params prm;
     pb200_default_params(&prm);
     int gpus = 1, first_device = 0;
+    bool peer_mode = true; // multi-GPU: halos and sums through peer memory inside the kernels (else NCCL calls per iteration)
     std::string dump, json;
     std::vector<const char *> pos;
     for (int i = 1; i < argc; ++i) {
@@ -88,6 +90,7 @@ int main(int argc, char **argv) {
         else if (a == "--trace") { need(1); prm.trace_len = atoi(argv[++i]); }
         else if (a == "--check-every") { need(1); prm.check_every = atoi(argv[++i]); }
         else if (a == "--no-graph") prm.use_graph = 0;
+        else if (a == "--comm") { need(1); peer_mode = std::string(argv[++i]) != "nccl"; }
         else if (a == "--dump") { need(1); dump = argv[++i]; }
         else if (a == "--json") { need(1); json = argv[++i]; }
         else if (a == "-h" || a == "--help") { usage(); return 0; }
@@ -125,6 +128,8 @@ int main(int argc, char **argv) {
         std::cerr << "poisson_b200: " << pb200_last_error() << "\n";
         return 1;
     }
+    std::vector<uint8_t> blobs(static_cast<size_t>(gpus) * 256);
+    std::atomic<int> exported{0}, failed{0};
     auto rank_main = [&](int rank) {
         pb200_params p = prm;
         p.nranks = gpus;
@@ -136,7 +141,15 @@ int main(int argc, char **argv) {
         };
         pb200_status st = pb200_create(&p, &solvers[rank]);
         if (st != PB200_OK) return fail(st);
-        if (gpus > 1 && (st = pb200_attach_comm(solvers[rank], uid)) != PB200_OK) return fail(st);
+        if (gpus > 1 && (st = pb200_attach_comm(solvers[rank], uid)) != PB200_OK) { failed = 1; return fail(st); }
+        if (gpus > 1 && peer_mode) { // every rank publishes where its mailbox / residual live, then maps the others'
+            st = pb200_peer_export(solvers[rank], blobs.data() + 256 * rank);
+            if (st != PB200_OK) failed = 1;
+            ++exported;
+            while (exported.load() < gpus && !failed.load()) std::this_thread::yield();
+            if (failed.load()) return fail(st != PB200_OK ? st : PB200_ERR_COMM);
+            if ((st = pb200_peer_attach(solvers[rank], blobs.data(), gpus)) != PB200_OK) return fail(st);
+        }
         if ((st = pb200_solve(solvers[rank], &results[rank])) != PB200_OK) return fail(st);
         if (!w.empty() && (st = pb200_get_solution(solvers[rank], w.data(), N + 1)) != PB200_OK) return fail(st);
     };

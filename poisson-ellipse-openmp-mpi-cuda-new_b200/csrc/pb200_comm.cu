@@ -14,6 +14,7 @@
 
 #include <cstring>
 #include <dlfcn.h>
+#include <unistd.h>
 #include <mutex>
 #include <nccl.h>
 
@@ -175,6 +176,110 @@ void Solver::exchange_r_halo() {
     acc(n.GroupEnd());
     if (r != ncclSuccess && comm->async_err == ncclSuccess) comm->async_err = r;
     if (cols) unpack_cols_kernel<<<nbk, tb, 0, stream>>>(f.r, g.nx, g.pitch, g.ny, comm->recv_lo, comm->recv_hi);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Peer-memory mode. Every rank exports where its mailbox and its r array live; after the host has handed every rank
+// all exports (MPI_Allgather / torch all_gather / shared memory between threads), peer_attach maps them: CUDA IPC
+// for ranks in other processes, plain pointers plus peer access for ranks that are threads of this process.
+namespace {
+struct PeerBlob {
+    int magic, pid, dev, rank;
+    int nx, ny, pitch, pad;
+    void *r_ptr, *mail_ptr;
+    cudaIpcMemHandle_t h_r, h_mail;
+};
+static_assert(sizeof(PeerBlob) <= 256, "blob fits the 256 bytes of the C ABI");
+} // namespace
+
+pb200_status Solver::peer_export(uint8_t blob[256]) {
+    if (prm.nranks <= 1) { set_error("peer mode needs nranks > 1"); return PB200_ERR_INVALID; }
+    if (prm.nranks > MAX_RANKS) { set_error("peer mode supports up to %d ranks", MAX_RANKS); return PB200_ERR_TOO_LARGE; }
+    CK(cudaSetDevice(dev));
+    if (!mail) {
+        CK(cudaMalloc(&mail, MAIL_DOUBLES * sizeof(double)));
+        CK(cudaMemset(mail, 0, MAIL_DOUBLES * sizeof(double)));
+    }
+    PeerBlob b{};
+    b.magic = 0x50423230;
+    b.pid = static_cast<int>(getpid());
+    b.dev = dev;
+    b.rank = prm.rank;
+    b.nx = f.g.nx;
+    b.ny = f.g.ny;
+    b.pitch = f.g.pitch;
+    b.r_ptr = f.r;
+    b.mail_ptr = mail;
+    CK(cudaIpcGetMemHandle(&b.h_r, f.r));
+    CK(cudaIpcGetMemHandle(&b.h_mail, mail));
+    std::memset(blob, 0, 256);
+    std::memcpy(blob, &b, sizeof(b));
+    return PB200_OK;
+}
+
+pb200_status Solver::peer_attach(const uint8_t *blobs, int nranks) {
+    if (nranks != prm.nranks || nranks > MAX_RANKS || !mail) { set_error("peer_attach: export first, pass nranks blobs"); return PB200_ERR_INVALID; }
+    CK(cudaSetDevice(dev));
+    peer_release();
+    const int me = static_cast<int>(getpid());
+    PeerBlob all[MAX_RANKS];
+    for (int q = 0; q < nranks; ++q) {
+        std::memcpy(&all[q], blobs + 256 * q, sizeof(PeerBlob));
+        if (all[q].magic != 0x50423230 || all[q].rank != q) { set_error("peer_attach: blob %d is not rank %d's export", q, q); return PB200_ERR_INVALID; }
+    }
+    auto map = [&](const PeerBlob &b, bool want_r, double **mail_out, double **r_out) -> pb200_status {
+        *r_out = nullptr;
+        if (b.rank == prm.rank) {
+            *mail_out = mail;
+            *r_out = f.r;
+        } else if (b.pid == me) { // a thread of this process: same address space
+            if (b.dev != dev) {
+                cudaError_t e = cudaDeviceEnablePeerAccess(b.dev, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CK(e);
+                cudaGetLastError();
+            }
+            *mail_out = static_cast<double *>(b.mail_ptr);
+            *r_out = static_cast<double *>(b.r_ptr);
+        } else {
+            void *pm = nullptr, *pr = nullptr;
+            CK(cudaIpcOpenMemHandle(&pm, b.h_mail, cudaIpcMemLazyEnablePeerAccess));
+            ipc_opened.push_back(pm);
+            *mail_out = static_cast<double *>(pm);
+            if (want_r) {
+                CK(cudaIpcOpenMemHandle(&pr, b.h_r, cudaIpcMemLazyEnablePeerAccess));
+                ipc_opened.push_back(pr);
+                *r_out = static_cast<double *>(pr);
+            }
+        }
+        return PB200_OK;
+    };
+    const int px = prm.rank % Px, py = prm.rank / Px; // S4:338-344
+    const int left = px > 0 ? prm.rank - 1 : -1, right = px < Px - 1 ? prm.rank + 1 : -1;
+    const int down = py > 0 ? prm.rank - Px : -1, up = py < Py - 1 ? prm.rank + Px : -1;
+    pv = PeerView{};
+    pv.nranks = nranks;
+    pv.rank = prm.rank;
+    for (int q = 0; q < nranks; ++q) {
+        const bool nb = (q == left || q == right || q == down || q == up);
+        double *rq = nullptr;
+        pb200_status st = map(all[q], nb, &pv.mail[q], &rq);
+        if (st != PB200_OK) return st;
+        if (q == left) { pv.r_left = rq; pv.nx_left = all[q].nx; }
+        if (q == right) pv.r_right = rq;
+        if (q == down) { pv.r_down = rq; pv.ny_down = all[q].ny; pv.pitch_down = all[q].pitch; }
+        if (q == up) { pv.r_up = rq; pv.pitch_up = all[q].pitch; }
+    }
+    peer_ready = true;
+    c.multi = 2;
+    if (graph_exec) { cudaGraphExecDestroy(graph_exec); graph_exec = nullptr; }
+    return PB200_OK;
+}
+
+void Solver::peer_release() {
+    for (void *p : ipc_opened) cudaIpcCloseMemHandle(p);
+    ipc_opened.clear();
+    peer_ready = false;
+    if (c.multi == 2) c.multi = 1;
 }
 
 pb200_status Solver::reduce_norms_host(double *) {

@@ -55,7 +55,8 @@ struct Consts {
     double delta;              // S4:1006
     int norm_mode;             // 0 weighted (S4:897), 1 stage0 (S0:154)
     int fixed;                 // 1: delta test does not stop the loop
-    int multi;                 // 1: scalars are all-reduced between kernels, finalize runs separately
+    int multi;                 // 0: one GPU. 1: scalars all-reduced by NCCL between kernels, finalize_kernel runs the tail.
+                               // 2: scalars and halos travel through peer memory inside K1/K2 (PeerView)
     int trace_len;
     long long max_iter;        // S4:1007 (or fixed_iters): enforced on the device
     // Coefficient classes: a, b are 1.0 (class 0) or 1/eps (class 1) everywhere except on the
@@ -95,7 +96,54 @@ struct Ctl {
     unsigned int ticket[2];
 };
 
-enum { STOP_MAX_ITER = 0, STOP_CONVERGED = 1, STOP_DENOM = 2 };
+enum { STOP_MAX_ITER = 0, STOP_CONVERGED = 1, STOP_DENOM = 2, STOP_COMM_TIMEOUT = 3 };
+
+// ------------------------------------------------------------------------------------------
+// Peer-memory communication (multi == 2): every rank maps every other rank's mailbox and its neighbours' r arrays
+// (CUDA IPC between processes, peer access between threads) and the iteration kernels do the exchange themselves:
+//   * the last block of K1 / K2 stores this rank's partial sums into EVERY rank's mailbox, fences, raises a flag, then
+//     waits until all flags of its own mailbox show the current iteration and adds the partials in rank order -- an
+//     all-reduce made of NVLink stores, one thread per GPU spinning on local memory, no NCCL call, graph-replayable;
+//   * K2 stores the new r of its boundary rows / columns straight into the neighbours' ring cells.
+// Replaces MPI_Allreduce (S4:872, 893, 926) and exchange_halos_2d_gpu (S4:331-500).
+constexpr int MAX_RANKS = 8;            // one NVSwitch box
+constexpr int MAIL_DOUBLES = 64;        // den[2][8] | dif[2][8] | zr[2][8] | flag_k1[8] | flag_k2[8]
+constexpr int MAIL_DEN = 0, MAIL_DIF = 16, MAIL_ZR = 32, MAIL_FLAG1 = 48, MAIL_FLAG2 = 56;
+
+struct PeerView {
+    int nranks, rank;
+    double *mail[MAX_RANKS];                    // every rank's mailbox (own included)
+    double *r_left, *r_right, *r_down, *r_up;   // neighbours' r arrays; null = no neighbour on that side
+    int nx_left;                                // the left neighbour's ring row nx_left+1 receives my row 1
+    int ny_down, pitch_down, pitch_up;          // the lower neighbour's ring column ny_down+1 receives my column 1
+};
+
+// One thread: publish nv values (slots at offsets off[v]) for iteration k to every rank, then wait for everyone's and
+// return the rank-ordered sums. False if a peer does not show up within ~2 s (the caller stops the solve).
+__device__ __forceinline__ bool peer_allreduce(const PeerView &pv, const int flag_off, const unsigned long long k, const int nv,
+                                               const int *off, const double *vals, double *sums) {
+    const int par = (int)(k & 1ull) * MAX_RANKS;
+    for (int q = 0; q < pv.nranks; ++q)
+        for (int v = 0; v < nv; ++v) pv.mail[q][off[v] + par + pv.rank] = vals[v];
+    __threadfence_system();
+    for (int q = 0; q < pv.nranks; ++q)
+        *reinterpret_cast<volatile unsigned long long *>(pv.mail[q] + flag_off + pv.rank) = k;
+    const volatile unsigned long long *flags = reinterpret_cast<const volatile unsigned long long *>(pv.mail[pv.rank] + flag_off);
+    const long long t0 = clock64();
+    for (int q = 0; q < pv.nranks; ++q)
+        while (flags[q] < k) {
+            if (clock64() - t0 > 4000000000ll) return false;
+            __nanosleep(64);
+        }
+    __threadfence_system();
+    const volatile double *mine = pv.mail[pv.rank];
+    for (int v = 0; v < nv; ++v) {
+        double s = 0.0;
+        for (int q = 0; q < pv.nranks; ++q) s += mine[off[v] + par + q]; // rank order, like the reference's MPI_SUM
+        sums[v] = s;
+    }
+    return true;
+}
 
 // ------------------------------------------------------------------------------------------
 // small helpers
@@ -143,7 +191,7 @@ __device__ __forceinline__ bool grid_reduce(double (&v)[NV], double *partials, u
             for (int w = 0; w < THREADS / 32; ++w) s += s_w[k][w];
             __stcg(&partials[(size_t)k * nblocks + bid], s);
         }
-        __threadfence();
+        __threadfence_system(); // system scope: K2's boundary stores may have gone to a peer GPU
         unsigned t = atomicAdd(ticket, 1u);
         s_last = (t == nblocks - 1);
     }
@@ -344,7 +392,7 @@ __global__ void __launch_bounds__(INIT_THREADS) init_kernel(const InitArgs A) {
     if (grid_reduce<1, INIT_THREADS>(acc, A.partials, &A.ctl->ticket[1], tot)) {
         const double zr = tot[0] * A.c.h1 * A.c.h2; // S3:191
         A.ctl->red[2] = zr;
-        if (!A.c.multi) A.ctl->zr_old = zr; // S4:838-843
+        if (A.c.multi == 0) A.ctl->zr_old = zr; // S4:838-843 (multi-GPU: after the NCCL all-reduce, finalize_kernel)
     }
 }
 
@@ -415,6 +463,7 @@ struct K1Args {
     Geom g;
     Consts c;
     int wn; // warp windows per row: ceil(ny / 124)
+    PeerView pv; // multi == 2
 };
 
 struct K2Args {
@@ -428,6 +477,7 @@ struct K2Args {
     Geom g;
     Consts c;
     int wn;
+    PeerView pv; // multi == 2
 };
 
 struct V4 {
@@ -824,7 +874,17 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
     if (grid_reduce<1, K1_THREADS>(acc, A.partials, &ctl->ticket[0], tot)) {
         ctl->red[0] = tot[0] * h1 * h2; // S3:191: sum * h1 * h2
         ctl->iter = ctl->iter + 1;      // S4:847-848: k
-        if (!A.c.multi) ctl->denom = ctl->red[0];
+        if (A.c.multi == 0) ctl->denom = ctl->red[0];
+        if (A.c.multi == 2) { // S4:872: the sum over ranks, through peer memory
+            const int off[1] = {MAIL_DEN};
+            double sum[1];
+            if (peer_allreduce(A.pv, MAIL_FLAG1, (unsigned long long)ctl->iter, 1, off, &ctl->red[0], sum)) ctl->denom = sum[0];
+            else {
+                ctl->status = STOP_COMM_TIMEOUT;
+                __threadfence();
+                ctl->done = 1;
+            }
+        }
     }
 }
 
@@ -875,7 +935,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    const double denom = A.c.multi ? ctl->red[0] : ctl->denom;
+    const double denom = (A.c.multi == 1) ? ctl->red[0] : ctl->denom;
     const bool brk = (A.c.norm_mode == 1) ? (denom < 1e-15) : (fabs(denom) < 1e-15); // S0:128 | S4:876
     if (brk) {
         if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -990,6 +1050,16 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
             }
             st4_mask(wb + (size_t)i * P, wn, L.own);
             st4_mask(rb + (size_t)i * P, rn, L.own);
+            if (A.c.multi == 2) { // halo of r (S4:361-398): boundary cells go straight into the neighbours' rings
+                if (i == 1 && A.pv.r_left) st4_mask(A.pv.r_left + (size_t)(A.pv.nx_left + 1) * P + L.c0, rn, L.own);
+                if (i == g.nx && A.pv.r_right) st4_mask(A.pv.r_right + L.c0, rn, L.own);
+#pragma unroll
+                for (int k = 0; k < LW; ++k) {
+                    if (A.pv.r_down && L.c0 + k == 1 && ((L.own >> k) & 1u))
+                        A.pv.r_down[(size_t)i * A.pv.pitch_down + A.pv.ny_down + 1] = rn.v[k];
+                    if (A.pv.r_up && L.c0 + k == g.ny && ((L.own >> k) & 1u)) A.pv.r_up[(size_t)i * A.pv.pitch_up] = rn.v[k];
+                }
+            }
             pc = cur.pn;
             cls_c = cur.cls;
         };
@@ -1009,7 +1079,18 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         const double zr = tot[1] * A.c.h1 * A.c.h2; // S3:191
         ctl->red[1] = tot[0];
         ctl->red[2] = zr;
-        if (!A.c.multi) finalize_iteration(ctl, A.c, A.trace, alpha, tot[0], zr);
+        if (A.c.multi == 0) finalize_iteration(ctl, A.c, A.trace, alpha, tot[0], zr);
+        if (A.c.multi == 2) { // S4:893, 926: both sums over ranks, through peer memory; every rank then runs the same tail
+            const int off[2] = {MAIL_DIF, MAIL_ZR};
+            double sum[2];
+            if (peer_allreduce(A.pv, MAIL_FLAG2, (unsigned long long)ctl->iter, 2, off, &ctl->red[1], sum))
+                finalize_iteration(ctl, A.c, A.trace, alpha, sum[0], sum[1]);
+            else {
+                ctl->status = STOP_COMM_TIMEOUT;
+                __threadfence();
+                ctl->done = 1;
+            }
+        }
     }
 }
 

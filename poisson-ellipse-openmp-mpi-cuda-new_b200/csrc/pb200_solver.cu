@@ -168,6 +168,8 @@ pb200_status Fields::allocate(const Geom &geom) {
 
 Solver::~Solver() {
     if (dev >= 0) cudaSetDevice(dev);
+    peer_release();
+    if (mail) cudaFree(mail);
     destroy_comm();
     if (graph_exec) cudaGraphExecDestroy(graph_exec);
     for (auto &e : ev_poll) if (e) cudaEventDestroy(e);
@@ -315,6 +317,7 @@ K1Args Solver::k1_args(long long k) const {
     a.g = f.g;
     a.c = c;
     a.wn = wn;
+    a.pv = pv;
     return a;
 }
 
@@ -333,6 +336,7 @@ K2Args Solver::k2_args(long long k) const {
     a.g = f.g;
     a.c = c;
     a.wn = wn;
+    a.pv = pv;
     return a;
 }
 
@@ -364,16 +368,16 @@ void Solver::launch_init() {
 
 void Solver::launch_iteration(long long k, bool first) {
     launch_k1(k1_args(k), first);
-    if (c.multi) allreduce(0, 1);
+    if (c.multi == 1) allreduce(0, 1);
     launch_k2(k2_args(k));
-    if (c.multi) {
+    if (c.multi == 1) { // NCCL mode; in peer-memory mode (2) the two kernels exchange everything themselves
         exchange_r_halo();
         allreduce(1, 2);
         finalize_kernel<<<1, 1, 0, stream>>>(ctl, c, trace, 0);
     }
 }
 
-int Solver::kernels_per_iteration() const { return c.multi ? 3 + halo_kernels_per_iteration() : 2; }
+int Solver::kernels_per_iteration() const { return c.multi == 1 ? 3 + halo_kernels_per_iteration() : 2; }
 
 pb200_status Solver::solve(pb200_result *res) {
     const double t0 = now_s();
@@ -388,6 +392,9 @@ pb200_status Solver::solve(pb200_result *res) {
     // ---- init (S4:803-843): w = 0 and r = B were written by setup; zr_old = (D^-1 r, r)
     CK(cudaMemsetAsync(ctl, 0, sizeof(Ctl), stream));
     CK(cudaMemsetAsync(norms, 0, 4 * sizeof(double), stream));
+    // peer-memory mode: clear the mailbox; the NCCL all-reduce of the start-up (z,r) below doubles as the barrier that
+    // keeps any rank from posting into a mailbox that has not been cleared yet
+    if (c.multi == 2) CK(cudaMemsetAsync(mail, 0, MAIL_DOUBLES * sizeof(double), stream));
     launch_init();
     ++launches;
     if (c.multi) {
@@ -405,9 +412,9 @@ pb200_status Solver::solve(pb200_result *res) {
         check = static_cast<int>(std::min(64.0, std::max(2.0, 250e-6 / t_it)));
     }
     check += check & 1; // even: graph replays cover two iterations
-    // Graph replay is single-GPU only: with NCCL collectives captured in the graph the replay hung on this
-    // stack (NCCL 2.27.3 / driver 580, 2 ranks); multi-GPU iterations are launched directly.
-    const bool use_graph = prm.use_graph != 0 && !c.multi;
+    // No graph replay in NCCL mode: with NCCL collectives captured in the graph the replay hung on this stack
+    // (NCCL 2.27.3 / driver 580, 2 ranks). In peer-memory mode the iteration is two plain kernels and is replayed.
+    const bool use_graph = prm.use_graph != 0 && c.multi != 1;
     CK(cudaEventRecord(ev_start, stream));
     long long k = 1;
     launch_iteration(k, true); // iteration 1: p = z (S4:830)
@@ -473,6 +480,7 @@ pb200_status Solver::solve(pb200_result *res) {
     const Ctl &hc = h_ctl[0];
     solved = true;
     last_iter = hc.iter;
+    if (hc.status == STOP_COMM_TIMEOUT) { set_error("a peer rank did not answer within the in-kernel time limit (peer-memory mode)"); return PB200_ERR_COMM; }
     if (res) {
         std::memset(res, 0, sizeof(*res));
         res->iterations = hc.iter;

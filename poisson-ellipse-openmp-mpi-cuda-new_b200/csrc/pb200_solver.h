@@ -3,6 +3,8 @@
 #include "../../include/poisson_b200.h"
 #include "pb200_kernels.cuh"
 
+#include <vector>
+
 namespace pb200 {
 
 extern thread_local char g_err[512];
@@ -64,6 +66,11 @@ struct Solver {
     bool solved = false;
     bool coefficients_ready = false;
     Comm *comm = nullptr;
+    // peer-memory mode (pb200_comm.cu): mailbox of this rank, views of the peers
+    double *mail = nullptr;
+    PeerView pv{};
+    bool peer_ready = false;
+    std::vector<void *> ipc_opened;
 
     ~Solver();
     pb200_status create(const pb200_params &params);
@@ -89,6 +96,9 @@ struct Solver {
     void exchange_r_halo();               // boundary rows/columns of r -> neighbours' ring
     int halo_kernels_per_iteration() const;
     pb200_status reduce_norms_host(double h_norms[4]);
+    pb200_status peer_export(uint8_t blob[256]);
+    pb200_status peer_attach(const uint8_t *blobs, int nranks);
+    void peer_release();
 };
 
 pb200_status comm_unique_id(uint8_t id_out[128]);

@@ -62,6 +62,19 @@ def test_results_do_not_depend_on_gpu_count(tmp_path, golden, M, N, gpus, extra)
     np.testing.assert_allclose(wp, w1, rtol=0, atol=1e-11)
 
 
+@pytest.mark.parametrize("M,N,gpus,extra", [(400, 600, 2, ()), (400, 600, 2, ("--grid", "2x1")), (37, 53, 2, ()),
+                                            (400, 600, 4, ()), (400, 600, 8, ())])
+def test_peer_memory_and_nccl_modes_agree_bitwise(tmp_path, M, N, gpus, extra):
+    """The default multi-GPU mode moves halos and partial sums through peer memory inside the kernels; --comm nccl
+    uses NCCL calls between the kernels. Same arithmetic, same rank-ordered sums: identical results."""
+    need(gpus)
+    _, a, wa = run_cli(tmp_path, M, N, gpus, extra + ("--comm", "peer"))
+    _, b, wb = run_cli(tmp_path, M, N, gpus, extra + ("--comm", "nccl"))
+    assert a["iterations"] == b["iterations"]
+    assert abs(a["w_norm_E"] - b["w_norm_E"]) <= 1e-12 * abs(b["w_norm_E"])
+    np.testing.assert_allclose(wa, wb, rtol=0, atol=1e-12)
+
+
 def test_multi_gpu_fixed_iterations_and_no_graph(tmp_path):
     need(2)
     _, a, wa = run_cli(tmp_path, 300, 200, 2, ("--fixed-iters", "37"))
