@@ -171,7 +171,8 @@ __device__ __forceinline__ double warp_sum(double v) {
 // "last block sums all block partials in index order" pass. Returns true in thread 0 of the
 // last block with the grid totals in out[0..NV). partials: [NV][nblocks].
 template <int NV, int THREADS>
-__device__ __forceinline__ bool grid_reduce(double (&v)[NV], double *partials, unsigned int *ticket, double (&out)[NV]) {
+__device__ __forceinline__ bool grid_reduce(double (&v)[NV], double *partials, unsigned int *ticket, double (&out)[NV],
+                                            const bool system_scope = false) {
     __shared__ double s_w[NV][THREADS / 32];
     __shared__ bool s_last;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -191,7 +192,8 @@ __device__ __forceinline__ bool grid_reduce(double (&v)[NV], double *partials, u
             for (int w = 0; w < THREADS / 32; ++w) s += s_w[k][w];
             __stcg(&partials[(size_t)k * nblocks + bid], s);
         }
-        __threadfence_system(); // system scope: K2's boundary stores may have gone to a peer GPU
+        if (system_scope) __threadfence_system(); // this block's boundary stores may have gone to a peer GPU
+        else __threadfence();
         unsigned t = atomicAdd(ticket, 1u);
         s_last = (t == nblocks - 1);
     }
@@ -1024,6 +1026,10 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
             }
         }
 
+        // peer-memory mode: does this warp's band / window touch a side that has a neighbour block? (warp-uniform)
+        const bool halo_out = A.c.multi == 2 &&
+                              ((L.i_lo == 1 && A.pv.r_left) || (L.i_hi == g.nx && A.pv.r_right) || (L.wcol == 0 && A.pv.r_down) ||
+                               (L.s + K1_OWN >= g.ny && A.pv.r_up));
         auto row_step = [&](const int i, const RowIn &cur) {
             const bool bad_n = !SAFE && range_bad4(cur.pn);
             const bool slow = __any_sync(0xffffffffu, bad_c | bad_n);
@@ -1050,7 +1056,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
             }
             st4_mask(wb + (size_t)i * P, wn, L.own);
             st4_mask(rb + (size_t)i * P, rn, L.own);
-            if (A.c.multi == 2) { // halo of r (S4:361-398): boundary cells go straight into the neighbours' rings
+            if (halo_out) { // halo of r (S4:361-398): boundary cells go straight into the neighbours' rings
                 if (i == 1 && A.pv.r_left) st4_mask(A.pv.r_left + (size_t)(A.pv.nx_left + 1) * P + L.c0, rn, L.own);
                 if (i == g.nx && A.pv.r_right) st4_mask(A.pv.r_right + L.c0, rn, L.own);
 #pragma unroll
@@ -1075,7 +1081,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         for (int r = 0; r < part.cta_rows; ++r) row_sync(r);
 
     double tot[2];
-    if (grid_reduce<2, K2_THREADS>(acc, A.partials, &ctl->ticket[1], tot)) {
+    if (grid_reduce<2, K2_THREADS>(acc, A.partials, &ctl->ticket[1], tot, A.c.multi == 2)) {
         const double zr = tot[1] * A.c.h1 * A.c.h2; // S3:191
         ctl->red[1] = tot[0];
         ctl->red[2] = zr;
