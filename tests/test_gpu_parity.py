@@ -80,10 +80,12 @@ def test_setup_other_ellipse_and_eps(oracle):
 
 # --------------------------------------------------------------------------------------------
 # operators on seeded inputs; shapes chosen to hit every edge of the kernel's tiling
-# (62-column warp windows, 8-row segments, 2-column vectors, single row / single column)
+# (124-column warp windows of 4-column lanes, 4-warp CTAs = 496 columns, 3-row pieces in these entry points,
+# single row / single column)
 
-SHAPES = [(39, 39), (1, 1), (1, 70), (70, 1), (2, 2), (7, 61), (8, 62), (9, 63), (17, 64), (16, 123), (33, 124),
-          (5, 125), (12, 495), (11, 496), (10, 497), (64, 1000), (130, 67)]
+SHAPES = [(39, 39), (1, 1), (1, 70), (70, 1), (2, 2), (3, 3), (4, 5), (7, 61), (8, 62), (9, 63), (17, 64), (16, 123),
+          (33, 124), (5, 125), (4, 126), (7, 127), (6, 128), (5, 247), (3, 248), (9, 249), (10, 372), (12, 495),
+          (11, 496), (10, 497), (2, 500), (64, 1000), (130, 67)]
 
 
 @pytest.mark.parametrize("nx,ny", SHAPES)
