@@ -561,12 +561,15 @@ struct Part {
 };
 
 // CTA c takes CTA-window c % wcn (K1_WARPS adjacent warp windows) of band c / wcn, wcn = ceil(windows / K1_WARPS).
-__device__ __forceinline__ Part make_part(int cta, int warp, int ncta, int wn, int nx) {
+// `descending`: bands are handed out from the last row upwards. K1 sweeps up the rows and K2 sweeps back down, so each
+// kernel starts on the ~100 MB the previous one touched last and finds them in the 126 MB L2 instead of in HBM.
+__device__ __forceinline__ Part make_part(int cta, int warp, int ncta, int wn, int nx, bool descending = false) {
     Part p;
     const int wcn = (wn + K1_WARPS - 1) / K1_WARPS;
     const int nb = max(1, ncta / wcn);
-    const int b = cta / wcn;
-    p.wcol[0] = (cta - b * wcn) * K1_WARPS + warp;
+    const int bq = cta / wcn;
+    const int b = (descending && bq < nb) ? nb - 1 - bq : bq;
+    p.wcol[0] = (cta - bq * wcn) * K1_WARPS + warp;
     p.lo[0] = 1 + (int)(((long long)nx * b) / nb);
     p.hi[0] = (int)(((long long)nx * (b + 1)) / nb);
     p.cta_rows = (b < nb && p.lo[0] <= p.hi[0]) ? p.hi[0] - p.lo[0] + 1 : 0;
@@ -952,7 +955,11 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
     const double h1 = A.c.h1, h2 = A.c.h2, rh1 = A.c.rh1, rh2 = A.c.rh2, mih1 = A.c.mih1, mih2 = A.c.mih2;
     const double inv_eps = A.c.inv_eps;
 
+#ifndef PB200_NO_REVERSE
+    const Part part = make_part(blockIdx.x, warp_id, gridDim.x, A.wn, g.nx, true);
+#else
     const Part part = make_part(blockIdx.x, warp_id, gridDim.x, A.wn, g.nx);
+#endif
 
     double acc[2] = {0.0, 0.0};
     unsigned tcount = 0u;
