@@ -10,7 +10,7 @@
 //
 // Arithmetic contract: every element-wise expression keeps the reference's expression tree with
 // one rounding per operation (this file is compiled with -fmad=false; the only fused operations
-// are the explicit __fma_rn inside div_const, which implements a correctly rounded division).
+// are the explicit __fma_rn inside div_const_nocheck, which implements a correctly rounded division).
 //
 // Layout of a block (nx x ny interior cells, 1-cell ring): rows li = 0..nx+1, columns lj = 0..ny+1,
 // element (li,lj) at base[li*pitch + lj]; pitch is a multiple of 16 doubles so every row starts on
@@ -150,12 +150,6 @@ __device__ __forceinline__ bool peer_allreduce(const PeerView &pv, const int fla
 
 __device__ __forceinline__ double dmax_std(double a, double b) { return (a < b) ? b : a; } // std::max
 __device__ __forceinline__ double dmin_std(double a, double b) { return (b < a) ? b : a; } // std::min
-
-__device__ __forceinline__ double2 ld2(const double *__restrict__ base, size_t off, bool ok) {
-    double2 v = make_double2(0.0, 0.0);
-    if (ok) v = __ldg(reinterpret_cast<const double2 *>(base + off));
-    return v;
-}
 
 __device__ __forceinline__ double shfl_up1(double v) { return __shfl_up_sync(0xffffffffu, v, 1); }
 __device__ __forceinline__ double shfl_dn1(double v) { return __shfl_down_sync(0xffffffffu, v, 1); }
