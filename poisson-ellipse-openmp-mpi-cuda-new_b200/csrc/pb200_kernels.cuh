@@ -602,6 +602,34 @@ __device__ __forceinline__ Lane make_lane(const Geom &g, int lane, int warp, int
     return L;
 }
 
+// Exact coefficients of the "general" cells (cut by the ellipse) a row step needs. They are the only operands that do
+// not come through the shared-memory ring, so all of them are requested together, first thing in the step, behind one
+// warp vote: one exposed memory round trip on the few rows that have such cells, none elsewhere.
+struct Exc {
+    V4 a;  // a(row_a, c0+k) where its class is general
+    V4 bn; // b(row_b, c0+k+1): the cell right of face k (k = 3: the next lane's first column)
+    V4 D;  // D(row_d, c0+k)
+};
+
+__device__ __forceinline__ bool load_exceptions(const unsigned cls_a, const unsigned cls_b, const unsigned cls_r,
+                                                const unsigned cls_d, const int lane, const double *a_row,
+                                                const double *b_row, const double *D_row, Exc &e) {
+    const unsigned ga = cls_a & 0x02020202u;
+    const unsigned gb = (cls_b & 0x08080800u) | ((lane < 31) ? (cls_r & 0x08u) : 0u);
+    const unsigned kd = (cls_d >> 4) & 0x0f0f0f0fu;
+    const unsigned gd = kd & (kd >> 1) & (kd >> 2) & (kd >> 3) & 0x01010101u; // nibble == DCLS_GENERAL (15)
+    if (!__any_sync(0xffffffffu, (ga | gb | gd) != 0u)) return false;
+#pragma unroll
+    for (int k = 0; k < LW; ++k) {
+        e.a.v[k] = (ga & (0x02u << (8 * k))) ? __ldg(a_row + k) : 0.0;
+        e.D.v[k] = (gd & (0x01u << (8 * k))) ? __ldg(D_row + k) : 1.0;
+    }
+#pragma unroll
+    for (int k = 0; k < LW - 1; ++k) e.bn.v[k] = (gb & (0x08u << (8 * (k + 1)))) ? __ldg(b_row + k + 1) : 0.0;
+    e.bn.v[LW - 1] = (gb & 0x08u) ? __ldg(b_row + LW) : 0.0;
+    return true;
+}
+
 // The numerators of the eight face fluxes of a lane in one row, S4:527/531:
 //   nx[k] = a(i+1, c0+k) * (p(i+1, c0+k) - p(i, c0+k))          (x faces above the lane's cells)
 //   ny[k] = b(i, c0+k+1) * (p(i, c0+k+1) - p(i, c0+k))          (y faces right of the lane's cells)
@@ -610,7 +638,7 @@ __device__ __forceinline__ Lane make_lane(const Geom &g, int lane, int warp, int
 // or wholly outside (all classes 1: a = b = 1/eps) take warp-uniform shortcuts.
 __device__ __forceinline__ void flux_numerators(const V4 &pn, const V4 &pc, const double pr, const unsigned cls_n,
                                                 const unsigned cls_c, const unsigned cls_r, const int lane,
-                                                const double inv_eps, const double *a_n, const double *b_c, V4 &nx,
+                                                const double inv_eps, const bool have_exc, const Exc &exc, V4 &nx,
                                                 V4 &ny) {
 #pragma unroll
     for (int k = 0; k < LW; ++k) nx.v[k] = pn.v[k] - pc.v[k];
@@ -636,15 +664,14 @@ __device__ __forceinline__ void flux_numerators(const V4 &pn, const V4 &pc, cons
 #pragma unroll
     for (int k = 0; k < LW - 1; ++k) bn.v[k] = class_value(cls_c >> (8 * (k + 1) + 2), inv_eps);
     bn.v[LW - 1] = class_value(cls_r >> 2, inv_eps);
-    const unsigned general = (cls_n & 0x02020202u) | (cls_c & 0x08080800u) | ((lane < 31) ? (cls_r & 0x08u) : 0u);
-    if (__any_sync(0xffffffffu, general != 0u)) { // a cell cut by the ellipse: exact values from the full arrays
+    if (have_exc) { // cells cut by the ellipse: the exact values fetched at the top of the step
 #pragma unroll
         for (int k = 0; k < LW; ++k)
-            if (cls_n & (0x02u << (8 * k))) an.v[k] = __ldg(a_n + k);
+            if (cls_n & (0x02u << (8 * k))) an.v[k] = exc.a.v[k];
 #pragma unroll
         for (int k = 0; k < LW - 1; ++k)
-            if (cls_c & (0x08u << (8 * (k + 1)))) bn.v[k] = __ldg(b_c + k + 1);
-        if ((lane < 31) && (cls_r & 0x08u)) bn.v[LW - 1] = __ldg(b_c + LW);
+            if (cls_c & (0x08u << (8 * (k + 1)))) bn.v[k] = exc.bn.v[k];
+        if ((lane < 31) && (cls_r & 0x08u)) bn.v[LW - 1] = exc.bn.v[LW - 1];
     }
 #pragma unroll
     for (int k = 0; k < LW; ++k) {
@@ -668,9 +695,9 @@ __device__ __forceinline__ V4 xface_numerators(const V4 &pc, const V4 &pm, const
 
 // D^-1 r for the lane's four cells of one row (S4:559): D and RN(1/D) from the class table; one broadcast
 // table read when the whole warp sits in one diagonal class, per-cell reads otherwise; cells next to the
-// ellipse boundary (general class) divide by the stored D.
+// ellipse boundary (general class) divide by the stored D, passed in D_exc.
 template <bool SAFE>
-__device__ __forceinline__ V4 precond4(const V4 &r, const unsigned cls, const double2 *s_lut, const double *D_row) {
+__device__ __forceinline__ V4 precond4(const V4 &r, const unsigned cls, const double2 *s_lut, const V4 &D_exc) {
     V4 z;
     const unsigned kd = (cls >> 4) & 0x0f0f0f0fu;
     const unsigned k0 = __shfl_sync(0xffffffffu, kd, 0) & 0xfu;
@@ -691,7 +718,7 @@ __device__ __forceinline__ V4 precond4(const V4 &r, const unsigned cls, const do
         const unsigned kk = (kd >> (8 * k)) & 0xfu;
         const double2 DR = s_lut[kk];
         z.v[k] = slow ? precond_div(r.v[k], DR.x) : div_const_nocheck(r.v[k], DR.x, DR.y);
-        if (kk == DCLS_GENERAL) z.v[k] = precond_div(r.v[k], __ldg(D_row + k));
+        if (kk == DCLS_GENERAL) z.v[k] = precond_div(r.v[k], D_exc.v[k]);
     }
     return z;
 }
@@ -806,8 +833,8 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         };
 #pragma unroll
         for (int t = 0; t < STAGES; ++t) issue(t);
-        auto p_update = [&](const RowIn &in, int n) {
-            V4 z = precond4<SAFE>(in.r, in.cls, s_lut, Db + (size_t)n * P); // S4:559
+        auto p_update = [&](const RowIn &in, const V4 &D_exc) {
+            V4 z = precond4<SAFE>(in.r, in.cls, s_lut, D_exc); // S4:559
             if (!FIRST) {
 #pragma unroll
                 for (int k = 0; k < LW; ++k) z.v[k] = z.v[k] + beta * in.q.v[k]; // S4:675 (FIRST: p = z, S4:830)
@@ -816,11 +843,14 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         };
 
         // rows i_lo-1 and i_lo: p' of both, and the flux through the face between them
+        Exc exc;
         RowIn in = fetch(0);
-        const V4 pm = p_update(in, L.i_lo - 1);
+        load_exceptions(0u, 0u, 0u, in.cls, L.lane, ab, bb, Db + (size_t)(L.i_lo - 1) * P, exc);
+        const V4 pm = p_update(in, exc.D);
         if (L.i_lo == 1) st4_mask(pob, pm, L.pw); // ring row 0
         in = fetch(1);
-        V4 pc = p_update(in, L.i_lo);
+        load_exceptions(0u, 0u, 0u, in.cls, L.lane, ab, bb, Db + (size_t)L.i_lo * P, exc);
+        V4 pc = p_update(in, exc.D);
         unsigned cls_c = in.cls;
         st4_mask(pob + (size_t)L.i_lo * P, pc, L.pw);
         bool bad_c = !SAFE && (range_bad4(pm) || range_bad4(pc));
@@ -838,16 +868,17 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
 
         // one row: consumes the operands of row i+1, leaves p'(i+1), Fx(i+1/2) and the classes of row i+1
         auto row_step = [&](const int i, const RowIn &cur, const unsigned st_mask) {
-            const V4 pn = p_update(cur, i + 1);
+            const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
+            const bool have_exc = load_exceptions(cur.cls, cls_c, cls_r, cur.cls, L.lane, ab + (size_t)(i + 1) * P,
+                                                  bb + (size_t)i * P, Db + (size_t)(i + 1) * P, exc);
+            const V4 pn = p_update(cur, exc.D);
             st4_mask(pob + (size_t)(i + 1) * P, pn, st_mask);
             const bool bad_n = !SAFE && range_bad4(pn);
             const bool slow = __any_sync(0xffffffffu, bad_c | bad_n);
             bad_c = bad_n;
             const double pr = shfl_dn1(pc.v[0]); // right neighbour of the lane's last column
-            const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
             V4 nx, ny;
-            flux_numerators(pn, pc, pr, cur.cls, cls_c, cls_r, L.lane, inv_eps, ab + (size_t)(i + 1) * P,
-                            bb + (size_t)i * P, nx, ny);
+            flux_numerators(pn, pc, pr, cur.cls, cls_c, cls_r, L.lane, inv_eps, have_exc, exc, nx, ny);
             const V4 out = stencil_row<SAFE>(nx, ny, fxl, slow, h1, rh1, h2, rh2, mih1, mih2);
             if (apb) st4_mask(apb + (size_t)i * P, out, L.own);
 #pragma unroll
@@ -1037,9 +1068,11 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
             bad_c = bad_n;
             const double pr = shfl_dn1(pc.v[0]);
             const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
+            Exc exc;
+            const bool have_exc = load_exceptions(cur.cls, cls_c, cls_r, cls_c, L.lane, ab + (size_t)(i + 1) * P,
+                                                  bb + (size_t)i * P, Db + (size_t)i * P, exc);
             V4 nx, ny;
-            flux_numerators(cur.pn, pc, pr, cur.cls, cls_c, cls_r, L.lane, inv_eps, ab + (size_t)(i + 1) * P,
-                            bb + (size_t)i * P, nx, ny);
+            flux_numerators(cur.pn, pc, pr, cur.cls, cls_c, cls_r, L.lane, inv_eps, have_exc, exc, nx, ny);
             const V4 Ap = stencil_row<SAFE>(nx, ny, fxl, slow, h1, rh1, h2, rh2, mih1, mih2); // the expressions K1 used for (Ap,p)
             V4 wn, rn;
 #pragma unroll
@@ -1047,7 +1080,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
                 wn.v[k] = cur.w.v[k] + alpha * pc.v[k]; // S4:647
                 rn.v[k] = cur.r.v[k] - alpha * Ap.v[k]; // S4:648
             }
-            const V4 zn = precond4<SAFE>(rn, cls_c, s_lut, Db + (size_t)i * P); // S4:559
+            const V4 zn = precond4<SAFE>(rn, cls_c, s_lut, exc.D); // S4:559
 #pragma unroll
             for (int k = 0; k < LW; ++k) {
                 const bool own = (L.own >> k) & 1u;

@@ -210,7 +210,7 @@ int march_blocks(int resident_blocks, int wn, int nx) {
     const double resident = std::max(1, resident_blocks);
     int best_rows = 20;
     double best_cost = 1e300;
-    for (int rows = 4; rows <= 24; ++rows) {
+    for (int rows = 2; rows <= 24; ++rows) {
         const double waves = blocks_for(rows) / resident;
         const double cost = std::ceil(waves) * (rows + 2) / wave_gain(waves);
         if (cost < best_cost * 0.999) {
