@@ -338,6 +338,14 @@ __device__ __forceinline__ bool in_div_range(double v) {
     const unsigned e = hi >> 20;
     return (e - 183u <= 1440u) || ((hi | (unsigned)__double2loint(v)) == 0u);
 }
+// The same test as a 0/1 word, written without short-circuit operators so that four of them combine into straight-line
+// predicate logic (the marching kernels test every p' and r they produce).
+__device__ __forceinline__ unsigned out_of_div_range(double v) {
+    const unsigned hi = (unsigned)__double2hiint(v) & 0x7fffffffu;
+    const unsigned outside = ((hi >> 20) - 183u > 1440u) ? 1u : 0u;
+    const unsigned nonzero = ((hi | (unsigned)__double2loint(v)) != 0u) ? 1u : 0u;
+    return outside & nonzero;
+}
 
 // Correctly rounded x / h for a divisor h that is the same for many x, given rh = RN(1/h) (computed on the host).
 // q0 = RN(x*rh) is within 1.5 ulp of x/h; one residual step makes it faithful (<= 0.5 ulp + 2^-53 ulp);
@@ -438,6 +446,10 @@ constexpr int K1_THREADS = K1_WARPS * 32;
 #define PB200_STAGES 4
 #endif
 constexpr int K2_THREADS = K1_THREADS;
+#ifndef PB200_ROW_UNROLL
+#define PB200_ROW_UNROLL 1
+#endif
+constexpr int ROW_UNROLL = PB200_ROW_UNROLL; // row steps per trip of the marching loops
 // Operand rows reach the SM through the bulk-copy engine (cp.async.bulk -> shared memory, completion on an
 // mbarrier), STAGES rows ahead of the row being computed, one private ring per warp: the bytes in flight no
 // longer depend on registers, scoreboard slots or occupancy.
@@ -480,6 +492,11 @@ struct V4 {
     double v[LW];
 };
 
+// The warp's index in its CTA, taken from lane 0 so that the compiler knows it is the same in all lanes: everything
+// derived from it (ring and barrier addresses, the rows and window of the warp's piece, the source addresses of the
+// bulk copies) can then live in uniform registers.
+__device__ __forceinline__ int uniform_warp_id() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
@@ -491,6 +508,41 @@ __device__ __forceinline__ void bulk_g2s(unsigned dst, const void *src, unsigned
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
                  "l"(src), "r"(bytes), "r"(bar)
                  : "memory");
+}
+// One pipeline unit: arm the stage's mbarrier with the byte count and start the bulk copies of up to three operand
+// rows plus the class record, all from ONE elected lane of a converged warp. Everything here is warp-uniform (see
+// uniform_warp_id), so the addresses stay in uniform registers and the whole unit is a dozen instructions.
+template <int NROWS>
+__device__ __forceinline__ void issue_unit(unsigned dst, unsigned bar, const void *s0, const void *s1, const void *s2,
+                                           const void *cls) {
+    static_assert(NROWS >= 1 && NROWS <= 3, "one to three operand rows per unit");
+    if (NROWS == 1)
+        asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\t"
+                     "@p mbarrier.arrive.expect_tx.shared::cta.b64 _, [%1], %2;\n\t"
+                     "@p cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%3], %5, [%1];\n\t"
+                     "@p cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%6], [%4], %7, [%1];\n\t}" ::"r"(dst),
+                     "r"(bar), "r"(ROW_BYTES + CLS_WIN), "l"(s0), "l"(cls), "r"(ROW_BYTES), "r"(dst + 2 * ROW_BYTES),
+                     "r"(CLS_WIN)
+                     : "memory");
+    if (NROWS == 2)
+        asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\t"
+                     "@p mbarrier.arrive.expect_tx.shared::cta.b64 _, [%1], %2;\n\t"
+                     "@p cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%3], %6, [%1];\n\t"
+                     "@p cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%7], [%4], %6, [%1];\n\t"
+                     "@p cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%8], [%5], %9, [%1];\n\t}" ::"r"(dst),
+                     "r"(bar), "r"(2 * ROW_BYTES + CLS_WIN), "l"(s0), "l"(s1), "l"(cls), "r"(ROW_BYTES), "r"(dst + ROW_BYTES),
+                     "r"(dst + 2 * ROW_BYTES), "r"(CLS_WIN)
+                     : "memory");
+    if (NROWS == 3)
+        asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\t"
+                     "@p mbarrier.arrive.expect_tx.shared::cta.b64 _, [%1], %2;\n\t"
+                     "@p cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%3], %7, [%1];\n\t"
+                     "@p cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%8], [%4], %7, [%1];\n\t"
+                     "@p cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%9], [%5], %7, [%1];\n\t"
+                     "@p cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%10], [%6], %11, [%1];\n\t}" ::"r"(dst),
+                     "r"(bar), "r"(3 * ROW_BYTES + CLS_WIN), "l"(s0), "l"(s1), "l"(s2), "l"(cls), "r"(ROW_BYTES),
+                     "r"(dst + ROW_BYTES), "r"(dst + 2 * ROW_BYTES), "r"(dst + 3 * ROW_BYTES), "r"(CLS_WIN)
+                     : "memory");
 }
 __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
     asm volatile("{\n\t.reg .pred p;\n\tWAIT_LOOP:\n\t"
@@ -514,28 +566,24 @@ __device__ __forceinline__ V4 ldg4_nc(const double *p, bool ok) { // read-only f
     if (ok) asm("ld.global.nc.v4.f64 {%0,%1,%2,%3}, [%4];" : "=d"(x.v[0]), "=d"(x.v[1]), "=d"(x.v[2]), "=d"(x.v[3]) : "l"(p));
     return x;
 }
-// Branch-free predicated store of a lane's four columns: one 256-bit store when all four are writable
-// (mask == 15), else up to four 8-byte stores.
+// Store of a lane's four columns under a per-column mask: one 256-bit store when all four are writable (every lane
+// but the few on a window or block edge; the mask is loop-invariant, so the test is hoisted), else 8-byte stores.
 __device__ __forceinline__ void st4_mask(double *p, const V4 &x, const unsigned mask) {
-    asm volatile("{\n\t.reg .pred pa, p0, p1, p2, p3;\n\t.reg .b32 t;\n\t"
-                 "setp.eq.u32 pa, %5, 15;\n\t"
-                 "and.b32 t, %5, 1;\n\tsetp.ne.and.u32 p0, t, 0, !pa;\n\t"
-                 "and.b32 t, %5, 2;\n\tsetp.ne.and.u32 p1, t, 0, !pa;\n\t"
-                 "and.b32 t, %5, 4;\n\tsetp.ne.and.u32 p2, t, 0, !pa;\n\t"
-                 "and.b32 t, %5, 8;\n\tsetp.ne.and.u32 p3, t, 0, !pa;\n\t"
-                 "@pa st.global.v4.f64 [%0], {%1, %2, %3, %4};\n\t"
-                 "@p0 st.global.f64 [%0], %1;\n\t"
-                 "@p1 st.global.f64 [%0+8], %2;\n\t"
-                 "@p2 st.global.f64 [%0+16], %3;\n\t"
-                 "@p3 st.global.f64 [%0+24], %4;\n\t}"
-                 :: "l"(p), "d"(x.v[0]), "d"(x.v[1]), "d"(x.v[2]), "d"(x.v[3]), "r"(mask) : "memory");
+    if (mask == 15u) {
+        asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(p), "d"(x.v[0]), "d"(x.v[1]), "d"(x.v[2]), "d"(x.v[3])
+                     : "memory");
+    } else {
+#pragma unroll
+        for (int k = 0; k < LW; ++k)
+            if (mask & (1u << k)) p[k] = x.v[k];
+    }
 }
 
 __device__ __forceinline__ double class_value(unsigned k, double inv_eps) { return (k & 1u) ? inv_eps : 1.0; }
 
 // true when one of the four values is outside the window in which the fast divisions are proven (in_div_range)
 __device__ __forceinline__ bool range_bad4(const V4 &x) {
-    return !(in_div_range(x.v[0]) && in_div_range(x.v[1]) && in_div_range(x.v[2]) && in_div_range(x.v[3]));
+    return (out_of_div_range(x.v[0]) | out_of_div_range(x.v[1]) | out_of_div_range(x.v[2]) | out_of_div_range(x.v[3])) != 0u;
 }
 
 // What a lane knows about its place in the march (computed once per kernel).
@@ -569,15 +617,6 @@ __device__ __forceinline__ Part make_part(int cta, int warp, int ncta, int wn, i
     p.cta_rows = (b < nb && p.lo[0] <= p.hi[0]) ? p.hi[0] - p.lo[0] + 1 : 0;
     p.nsub = (p.cta_rows > 0 && p.wcol[0] < wn) ? 1 : 0;
     return p;
-}
-
-// Optional: keep the warps of a CTA on the same row (they then ask DRAM for adjacent 1 KB pieces of a row at the same
-// time). Every warp of the CTA, working or not, passes the same number of these barriers.
-#ifndef PB200_ROWSYNC
-#define PB200_ROWSYNC 0
-#endif
-__device__ __forceinline__ void row_sync(int r) {
-    if (PB200_ROWSYNC > 0 && (r % (PB200_ROWSYNC > 0 ? PB200_ROWSYNC : 1)) == 0) __syncthreads();
 }
 
 __device__ __forceinline__ Lane make_lane(const Geom &g, int lane, int warp, int wcol, int i_lo, int i_hi) {
@@ -764,7 +803,7 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
     __shared__ double2 s_lut[16];
     if (stopped(ctl)) return;
     const Geom g = A.g;
-    const int lane_id = threadIdx.x & 31, warp_id = threadIdx.x >> 5;
+    const int lane_id = threadIdx.x & 31, warp_id = uniform_warp_id();
     if (threadIdx.x < 16) s_lut[threadIdx.x] = make_double2(A.c.lutD[threadIdx.x], A.c.lutR[threadIdx.x]);
     if (lane_id == 0) {
 #pragma unroll
@@ -778,13 +817,11 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
     const Part part = make_part(blockIdx.x, warp_id, gridDim.x, A.wn, g.nx);
 
     double acc[1] = {0.0};
-    unsigned tcount = 0u; // pipeline units consumed so far by this warp: stage and mbarrier parity follow from it
-#pragma unroll 1
-    for (int sub = 0; sub < part.nsub; ++sub) {
-        const Lane L = make_lane(g, lane_id, warp_id, part.wcol[sub], part.lo[sub], part.hi[sub]);
+    if (part.nsub > 0) {
+        const Lane L = make_lane(g, lane_id, warp_id, part.wcol[0], part.lo[0], part.hi[0]);
         const size_t P = (size_t)g.pitch;
         const double *ab = A.a + L.c0, *bb = A.b + L.c0, *Db = A.D + L.c0;
-        double *pob = A.p_new + L.c0;
+        double *po_row = A.p_new + L.c0 + (size_t)(L.i_lo - 1) * P; // p' row being written (advanced by the stores)
         double *apb = A.Ap ? A.Ap + L.c0 : nullptr;
 
         struct RowIn {
@@ -793,46 +830,48 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         };
         // Operand pipeline: unit t is row (i_lo-1)+t; lane 0 asks the copy engine for r, p and the class record of
         // the warp's window, STAGES units ahead; the bytes land in this warp's ring and flip the stage's mbarrier.
-        const int row0 = L.i_lo - 1, nunits = L.i_hi - L.i_lo + 3;
-        unsigned char *ring = dyn_smem + (size_t)L.warp * STAGES * K1_STAGE_BYTES;
-        const unsigned ring_s = smem_u32(ring), bar_s = smem_u32(&s_bar[L.warp][0]);
-        const double *r_src = A.r + L.s, *q_src = A.p_old + L.s;
-        const unsigned char *c_src = A.cls + cls_index(g.cpitch, 0, L.wcol, 0);
-        auto issue = [&](int t) {
-            if (L.lane == 0 && t < nunits) {
-#ifdef PB200_FENCE_LANE0
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-#endif
-                const int st = (int)((tcount + (unsigned)t) & (STAGES - 1));
-                const size_t n = (size_t)(row0 + t);
-                const unsigned bar = bar_s + 8u * st, dst = ring_s + (unsigned)(st * K1_STAGE_BYTES);
-                mbar_expect_tx(bar, FIRST ? ROW_BYTES + CLS_WIN : K1_STAGE_BYTES);
-                bulk_g2s(dst, r_src + n * P, ROW_BYTES, bar);
-                if (!FIRST) bulk_g2s(dst + ROW_BYTES, q_src + n * P, ROW_BYTES, bar);
-                bulk_g2s(dst + 2 * ROW_BYTES, c_src + n * (size_t)g.cpitch, CLS_WIN, bar);
+        // Units are issued and consumed strictly in order, so a refill always goes into the stage just read: one
+        // cursor (stage offset, barrier offset, parity) serves both, and the sources are running pointers.
+        const int nunits = L.i_hi - L.i_lo + 3;
+        unsigned char *ring = dyn_smem + (size_t)warp_id * STAGES * K1_STAGE_BYTES;
+        const unsigned ring_s = smem_u32(ring), bar_s = smem_u32(&s_bar[warp_id][0]);
+        const size_t row_b = P * sizeof(double), cls_b = (size_t)g.cpitch;
+        const char *r_nx = reinterpret_cast<const char *>(A.r + L.s) + (size_t)(L.i_lo - 1) * row_b;
+        const char *q_nx = reinterpret_cast<const char *>(A.p_old + L.s) + (size_t)(L.i_lo - 1) * row_b;
+        const char *c_nx = reinterpret_cast<const char *>(A.cls + cls_index(g.cpitch, 0, L.wcol, 0)) + (size_t)(L.i_lo - 1) * cls_b;
+        int to_issue = nunits;
+        unsigned cur_off = 0u, cur_bar = 0u, cur_par = 0u; // stage being consumed: byte offset in the ring, barrier offset, parity
+        auto issue = [&](const unsigned off, const unsigned bar_off) { // next unit -> the stage at (off, bar_off)
+            if (to_issue > 0) {
+                if (FIRST) issue_unit<1>(ring_s + off, bar_s + bar_off, r_nx, nullptr, nullptr, c_nx);
+                else issue_unit<2>(ring_s + off, bar_s + bar_off, r_nx, q_nx, nullptr, c_nx);
+                r_nx += row_b;
+                q_nx += row_b;
+                c_nx += cls_b;
+                --to_issue;
             }
         };
-        auto fetch = [&](int t) {
+        auto fetch = [&]() {
             RowIn in;
-            const unsigned u = tcount + (unsigned)t;
-            const int st = (int)(u & (STAGES - 1));
-            mbar_wait(bar_s + 8u * st, (u / STAGES) & 1u);
-            const unsigned char *base = ring + st * K1_STAGE_BYTES;
-            in.r = lds4(base, L.lane);
-            if (!FIRST) in.q = lds4(base + ROW_BYTES, L.lane);
-            in.cls = *reinterpret_cast<const unsigned *>(base + 2 * ROW_BYTES + 4 * L.lane);
+            mbar_wait(bar_s + cur_bar, cur_par);
+            const unsigned char *base = ring + cur_off;
+            in.r = lds4(base, lane_id);
+            if (!FIRST) in.q = lds4(base + ROW_BYTES, lane_id);
+            in.cls = *reinterpret_cast<const unsigned *>(base + 2 * ROW_BYTES + 4 * lane_id);
             // Every lane has its copy; the stage may be refilled. The refill is written by the async proxy: without
             // the proxy fence it may overtake the generic-proxy reads above (observed: wrong, run-to-run varying
             // results on long solves).
             __syncwarp();
-#ifndef PB200_FENCE_LANE0
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-#endif
-            issue(t + STAGES);
+            issue(cur_off, cur_bar);
+            const bool wrap = cur_bar == 8u * (STAGES - 1);
+            cur_off = wrap ? 0u : cur_off + (unsigned)K1_STAGE_BYTES;
+            cur_bar = wrap ? 0u : cur_bar + 8u;
+            cur_par ^= wrap ? 1u : 0u;
             return in;
         };
 #pragma unroll
-        for (int t = 0; t < STAGES; ++t) issue(t);
+        for (int t = 0; t < STAGES; ++t) issue((unsigned)(t * K1_STAGE_BYTES), 8u * t);
         auto p_update = [&](const RowIn &in, const V4 &D_exc) {
             V4 z = precond4<SAFE>(in.r, in.cls, s_lut, D_exc); // S4:559
             if (!FIRST) {
@@ -844,15 +883,16 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
 
         // rows i_lo-1 and i_lo: p' of both, and the flux through the face between them
         Exc exc;
-        RowIn in = fetch(0);
-        load_exceptions(0u, 0u, 0u, in.cls, L.lane, ab, bb, Db + (size_t)(L.i_lo - 1) * P, exc);
+        RowIn in = fetch();
+        load_exceptions(0u, 0u, 0u, in.cls, lane_id, ab, bb, Db + (size_t)(L.i_lo - 1) * P, exc);
         const V4 pm = p_update(in, exc.D);
-        if (L.i_lo == 1) st4_mask(pob, pm, L.pw); // ring row 0
-        in = fetch(1);
-        load_exceptions(0u, 0u, 0u, in.cls, L.lane, ab, bb, Db + (size_t)L.i_lo * P, exc);
+        if (L.i_lo == 1) st4_mask(po_row, pm, L.pw); // ring row 0
+        po_row += P;
+        in = fetch();
+        load_exceptions(0u, 0u, 0u, in.cls, lane_id, ab, bb, Db + (size_t)L.i_lo * P, exc);
         V4 pc = p_update(in, exc.D);
         unsigned cls_c = in.cls;
-        st4_mask(pob + (size_t)L.i_lo * P, pc, L.pw);
+        st4_mask(po_row, pc, L.pw);
         bool bad_c = !SAFE && (range_bad4(pm) || range_bad4(pc));
         V4 fxl;
         {
@@ -869,16 +909,17 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         // one row: consumes the operands of row i+1, leaves p'(i+1), Fx(i+1/2) and the classes of row i+1
         auto row_step = [&](const int i, const RowIn &cur, const unsigned st_mask) {
             const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
-            const bool have_exc = load_exceptions(cur.cls, cls_c, cls_r, cur.cls, L.lane, ab + (size_t)(i + 1) * P,
+            const bool have_exc = load_exceptions(cur.cls, cls_c, cls_r, cur.cls, lane_id, ab + (size_t)(i + 1) * P,
                                                   bb + (size_t)i * P, Db + (size_t)(i + 1) * P, exc);
             const V4 pn = p_update(cur, exc.D);
-            st4_mask(pob + (size_t)(i + 1) * P, pn, st_mask);
+            po_row += P;
+            st4_mask(po_row, pn, st_mask);
             const bool bad_n = !SAFE && range_bad4(pn);
             const bool slow = __any_sync(0xffffffffu, bad_c | bad_n);
             bad_c = bad_n;
             const double pr = shfl_dn1(pc.v[0]); // right neighbour of the lane's last column
             V4 nx, ny;
-            flux_numerators(pn, pc, pr, cur.cls, cls_c, cls_r, L.lane, inv_eps, have_exc, exc, nx, ny);
+            flux_numerators(pn, pc, pr, cur.cls, cls_c, cls_r, lane_id, inv_eps, have_exc, exc, nx, ny);
             const V4 out = stencil_row<SAFE>(nx, ny, fxl, slow, h1, rh1, h2, rh2, mih1, mih2);
             if (apb) st4_mask(apb + (size_t)i * P, out, L.own);
 #pragma unroll
@@ -888,17 +929,10 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         };
 
         const unsigned last = (L.i_hi == g.nx) ? L.pw : 0u; // row i_hi+1 belongs to the next segment unless it is ring row nx+1
-#pragma unroll 1
-        for (int i = L.i_lo; i < L.i_hi; ++i) {
-            row_sync(i - L.i_lo);
-            row_step(i, fetch(i - L.i_lo + 2), L.pw);
-        }
-        row_sync(L.i_hi - L.i_lo);
-        row_step(L.i_hi, fetch(L.i_hi - L.i_lo + 2), last);
-        tcount += (unsigned)nunits;
+#pragma unroll ROW_UNROLL
+        for (int i = L.i_lo; i < L.i_hi; ++i) row_step(i, fetch(), L.pw);
+        row_step(L.i_hi, fetch(), last);
     }
-    if (part.nsub == 0)
-        for (int r = 0; r < part.cta_rows; ++r) row_sync(r); // a warp without a window still meets its CTA's barriers
 
     double tot[1];
     if (grid_reduce<1, K1_THREADS>(acc, A.partials, &ctl->ticket[0], tot)) {
@@ -957,7 +991,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
     __shared__ double2 s_lut[16];
     if (stopped(ctl)) return;
     const Geom g = A.g;
-    const int lane_id = threadIdx.x & 31, warp_id = threadIdx.x >> 5;
+    const int lane_id = threadIdx.x & 31, warp_id = uniform_warp_id();
     if (threadIdx.x < 16) s_lut[threadIdx.x] = make_double2(A.c.lutD[threadIdx.x], A.c.lutR[threadIdx.x]);
     if (lane_id == 0) {
 #pragma unroll
@@ -987,13 +1021,11 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
 #endif
 
     double acc[2] = {0.0, 0.0};
-    unsigned tcount = 0u;
-#pragma unroll 1
-    for (int sub = 0; sub < part.nsub; ++sub) {
-        const Lane L = make_lane(g, lane_id, warp_id, part.wcol[sub], part.lo[sub], part.hi[sub]);
+    if (part.nsub > 0) {
+        const Lane L = make_lane(g, lane_id, warp_id, part.wcol[0], part.lo[0], part.hi[0]);
         const size_t P = (size_t)g.pitch;
         const double *pb = A.p + L.c0, *ab = A.a + L.c0, *bb = A.b + L.c0, *Db = A.D + L.c0;
-        double *wb = A.w + L.c0, *rb = A.r + L.c0;
+        double *w_row = A.w + L.c0 + (size_t)L.i_lo * P, *r_row = A.r + L.c0 + (size_t)L.i_lo * P; // rows being written
 
         struct RowIn {
             V4 pn;         // p' of row i+1
@@ -1002,49 +1034,49 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         };
         // Operand pipeline (see k1_kernel): unit t = row i_lo+t brings p'(i+1), w(i), r(i) and the classes of row i+1.
         const int nunits = L.i_hi - L.i_lo + 1;
-        unsigned char *ring = dyn_smem + (size_t)L.warp * STAGES * K2_STAGE_BYTES;
-        const unsigned ring_s = smem_u32(ring), bar_s = smem_u32(&s_bar[L.warp][0]);
-        const double *p_src = A.p + L.s, *w_src = A.w + L.s, *r_src = A.r + L.s;
-        const unsigned char *c_src = A.cls + cls_index(g.cpitch, 0, L.wcol, 0);
-        auto issue = [&](int t) {
-            if (L.lane == 0 && t < nunits) {
-#ifdef PB200_FENCE_LANE0
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-#endif
-                const int st = (int)((tcount + (unsigned)t) & (STAGES - 1));
-                const size_t i = (size_t)(L.i_lo + t);
-                const unsigned bar = bar_s + 8u * st, dst = ring_s + (unsigned)(st * K2_STAGE_BYTES);
-                mbar_expect_tx(bar, K2_STAGE_BYTES);
-                bulk_g2s(dst, p_src + (i + 1) * P, ROW_BYTES, bar);
-                bulk_g2s(dst + ROW_BYTES, w_src + i * P, ROW_BYTES, bar);
-                bulk_g2s(dst + 2 * ROW_BYTES, r_src + i * P, ROW_BYTES, bar);
-                bulk_g2s(dst + 3 * ROW_BYTES, c_src + (i + 1) * (size_t)g.cpitch, CLS_WIN, bar);
+        unsigned char *ring = dyn_smem + (size_t)warp_id * STAGES * K2_STAGE_BYTES;
+        const unsigned ring_s = smem_u32(ring), bar_s = smem_u32(&s_bar[warp_id][0]);
+        const size_t row_b = P * sizeof(double), cls_b = (size_t)g.cpitch;
+        const char *p_nx = reinterpret_cast<const char *>(A.p + L.s) + (size_t)(L.i_lo + 1) * row_b;
+        const char *w_nx = reinterpret_cast<const char *>(A.w + L.s) + (size_t)L.i_lo * row_b;
+        const char *r_nx = reinterpret_cast<const char *>(A.r + L.s) + (size_t)L.i_lo * row_b;
+        const char *c_nx = reinterpret_cast<const char *>(A.cls + cls_index(g.cpitch, 0, L.wcol, 0)) + (size_t)(L.i_lo + 1) * cls_b;
+        int to_issue = nunits;
+        unsigned cur_off = 0u, cur_bar = 0u, cur_par = 0u;
+        auto issue = [&](const unsigned off, const unsigned bar_off) {
+            if (to_issue > 0) {
+                issue_unit<3>(ring_s + off, bar_s + bar_off, p_nx, w_nx, r_nx, c_nx);
+                p_nx += row_b;
+                w_nx += row_b;
+                r_nx += row_b;
+                c_nx += cls_b;
+                --to_issue;
             }
         };
-        auto fetch = [&](int t) {
+        auto fetch = [&]() {
             RowIn in;
-            const unsigned u = tcount + (unsigned)t;
-            const int st = (int)(u & (STAGES - 1));
-            mbar_wait(bar_s + 8u * st, (u / STAGES) & 1u);
-            const unsigned char *base = ring + st * K2_STAGE_BYTES;
-            in.pn = lds4(base, L.lane);
-            in.w = lds4(base + ROW_BYTES, L.lane);
-            in.r = lds4(base + 2 * ROW_BYTES, L.lane);
-            in.cls = *reinterpret_cast<const unsigned *>(base + 3 * ROW_BYTES + 4 * L.lane);
+            mbar_wait(bar_s + cur_bar, cur_par);
+            const unsigned char *base = ring + cur_off;
+            in.pn = lds4(base, lane_id);
+            in.w = lds4(base + ROW_BYTES, lane_id);
+            in.r = lds4(base + 2 * ROW_BYTES, lane_id);
+            in.cls = *reinterpret_cast<const unsigned *>(base + 3 * ROW_BYTES + 4 * lane_id);
             __syncwarp(); // see k1_kernel: reads first, proxy fence, then the refill
-#ifndef PB200_FENCE_LANE0
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-#endif
-            issue(t + STAGES);
+            issue(cur_off, cur_bar);
+            const bool wrap = cur_bar == 8u * (STAGES - 1);
+            cur_off = wrap ? 0u : cur_off + (unsigned)K2_STAGE_BYTES;
+            cur_bar = wrap ? 0u : cur_bar + 8u;
+            cur_par ^= wrap ? 1u : 0u;
             return in;
         };
 #pragma unroll
-        for (int t = 0; t < STAGES; ++t) issue(t);
+        for (int t = 0; t < STAGES; ++t) issue((unsigned)(t * K2_STAGE_BYTES), 8u * t);
 
         // rows i_lo-1 and i_lo of p', the classes of row i_lo, and the flux through the face between them
         const V4 pm = ldg4_nc(pb + (size_t)(L.i_lo - 1) * P, true);
         V4 pc = ldg4_nc(pb + (size_t)L.i_lo * P, true);
-        unsigned cls_c = __ldg(reinterpret_cast<const unsigned *>(A.cls + cls_index(g.cpitch, L.i_lo, L.wcol, 4 * L.lane)));
+        unsigned cls_c = __ldg(reinterpret_cast<const unsigned *>(A.cls + cls_index(g.cpitch, L.i_lo, L.wcol, 4 * lane_id)));
         bool bad_c = !SAFE && (range_bad4(pm) || range_bad4(pc));
         V4 fxl;
         {
@@ -1069,10 +1101,10 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
             const double pr = shfl_dn1(pc.v[0]);
             const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
             Exc exc;
-            const bool have_exc = load_exceptions(cur.cls, cls_c, cls_r, cls_c, L.lane, ab + (size_t)(i + 1) * P,
+            const bool have_exc = load_exceptions(cur.cls, cls_c, cls_r, cls_c, lane_id, ab + (size_t)(i + 1) * P,
                                                   bb + (size_t)i * P, Db + (size_t)i * P, exc);
             V4 nx, ny;
-            flux_numerators(cur.pn, pc, pr, cur.cls, cls_c, cls_r, L.lane, inv_eps, have_exc, exc, nx, ny);
+            flux_numerators(cur.pn, pc, pr, cur.cls, cls_c, cls_r, lane_id, inv_eps, have_exc, exc, nx, ny);
             const V4 Ap = stencil_row<SAFE>(nx, ny, fxl, slow, h1, rh1, h2, rh2, mih1, mih2); // the expressions K1 used for (Ap,p)
             V4 wn, rn;
 #pragma unroll
@@ -1088,8 +1120,10 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
                 acc[0] += own ? d * d : 0.0;
                 acc[1] += own ? zn.v[k] * rn.v[k] : 0.0; // S4:594
             }
-            st4_mask(wb + (size_t)i * P, wn, L.own);
-            st4_mask(rb + (size_t)i * P, rn, L.own);
+            st4_mask(w_row, wn, L.own);
+            st4_mask(r_row, rn, L.own);
+            w_row += P;
+            r_row += P;
             if (halo_out) { // halo of r (S4:361-398): boundary cells go straight into the neighbours' rings
                 if (i == 1 && A.pv.r_left) st4_mask(A.pv.r_left + (size_t)(A.pv.nx_left + 1) * P + L.c0, rn, L.own);
                 if (i == g.nx && A.pv.r_right) st4_mask(A.pv.r_right + L.c0, rn, L.own);
@@ -1104,15 +1138,9 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
             cls_c = cur.cls;
         };
 
-#pragma unroll 1
-        for (int i = L.i_lo; i <= L.i_hi; ++i) {
-            row_sync(i - L.i_lo);
-            row_step(i, fetch(i - L.i_lo));
-        }
-        tcount += (unsigned)nunits;
+#pragma unroll ROW_UNROLL
+        for (int i = L.i_lo; i <= L.i_hi; ++i) row_step(i, fetch());
     }
-    if (part.nsub == 0)
-        for (int r = 0; r < part.cta_rows; ++r) row_sync(r);
 
     double tot[2];
     if (grid_reduce<2, K2_THREADS>(acc, A.partials, &ctl->ticket[1], tot, A.c.multi == 2)) {
