@@ -48,6 +48,7 @@ struct Consts {
     double h1, h2;             // S4:691-692
     double rh1, rh2;           // RN(1/h1), RN(1/h2) for div_const
     double mih1, mih2;         // -1.0/h1, -1.0/h2 (S4:526, 530)
+    int pow2;                  // bit 0: h1 is a power of two, bit 1: h2 is (x / h is then the exact product x * rh)
     double h1h1, h2h2;         // h1*h1, h2*h2 (S4:556-557)
     double eps, inv_eps;       // S4:693; 1.0/eps (S4:169)
     double ell_k, ell_c;       // ellipse x^2 + (k y)^2 < 1; c = k*k (S4:33: 4.0)
@@ -766,7 +767,7 @@ __device__ __forceinline__ V4 precond4(const V4 &r, const unsigned cls, const do
 template <bool SAFE>
 __device__ __forceinline__ V4 stencil_row(const V4 &nx, const V4 &ny, V4 &fxl, const bool slow, const double h1,
                                           const double rh1, const double h2, const double rh2, const double mih1,
-                                          const double mih2) {
+                                          const double mih2, const int pow2) {
     V4 fx, fy, out;
     if (SAFE || slow) { // warp-uniform
 #pragma unroll
@@ -774,11 +775,34 @@ __device__ __forceinline__ V4 stencil_row(const V4 &nx, const V4 &ny, V4 &fxl, c
             fx.v[k] = __ddiv_rn(nx.v[k], h1);
             fy.v[k] = __ddiv_rn(ny.v[k], h2);
         }
-    } else {
+    } else if (pow2 == 0) {
 #pragma unroll
         for (int k = 0; k < LW; ++k) {
             fx.v[k] = div_const_nocheck(nx.v[k], h1, rh1);
             fy.v[k] = div_const_nocheck(ny.v[k], h2, rh2);
+        }
+    } else {
+        // A grid step that is a power of two (h1 = 2/M with M = 8192, 32768, ...): rh is exact and, inside the window
+        // the row has been tested for, the product x * rh neither overflows nor falls below the normal range, so it IS
+        // the IEEE quotient x / h -- one multiplication instead of five operations.
+        if (pow2 == 1) {
+#pragma unroll
+            for (int k = 0; k < LW; ++k) {
+                fx.v[k] = __dmul_rn(nx.v[k], rh1);
+                fy.v[k] = div_const_nocheck(ny.v[k], h2, rh2);
+            }
+        } else if (pow2 == 2) {
+#pragma unroll
+            for (int k = 0; k < LW; ++k) {
+                fx.v[k] = div_const_nocheck(nx.v[k], h1, rh1);
+                fy.v[k] = __dmul_rn(ny.v[k], rh2);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < LW; ++k) {
+                fx.v[k] = __dmul_rn(nx.v[k], rh1);
+                fy.v[k] = __dmul_rn(ny.v[k], rh2);
+            }
         }
     }
     const double fl = shfl_up1(fy.v[LW - 1]); // Fy left of the lane's first column = previous lane's last face
@@ -813,6 +837,7 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
     __syncthreads();
     const double h1 = A.c.h1, h2 = A.c.h2, rh1 = A.c.rh1, rh2 = A.c.rh2, mih1 = A.c.mih1, mih2 = A.c.mih2;
     const double inv_eps = A.c.inv_eps;
+    const int pow2 = A.c.pow2;
     const double beta = FIRST ? 0.0 : ctl->beta;
     const Part part = make_part(blockIdx.x, warp_id, gridDim.x, A.wn, g.nx);
 
@@ -920,7 +945,7 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
             const double pr = shfl_dn1(pc.v[0]); // right neighbour of the lane's last column
             V4 nx, ny;
             flux_numerators(pn, pc, pr, cur.cls, cls_c, cls_r, lane_id, inv_eps, have_exc, exc, nx, ny);
-            const V4 out = stencil_row<SAFE>(nx, ny, fxl, slow, h1, rh1, h2, rh2, mih1, mih2);
+            const V4 out = stencil_row<SAFE>(nx, ny, fxl, slow, h1, rh1, h2, rh2, mih1, mih2, pow2);
             if (apb) st4_mask(apb + (size_t)i * P, out, L.own);
 #pragma unroll
             for (int k = 0; k < LW; ++k) acc[0] += ((L.own >> k) & 1u) ? out.v[k] * pc.v[k] : 0.0; // S4:594
@@ -1013,6 +1038,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
     const double alpha = ctl->zr_old / denom; // S4:877
     const double h1 = A.c.h1, h2 = A.c.h2, rh1 = A.c.rh1, rh2 = A.c.rh2, mih1 = A.c.mih1, mih2 = A.c.mih2;
     const double inv_eps = A.c.inv_eps;
+    const int pow2 = A.c.pow2;
 
 #ifndef PB200_NO_REVERSE
     const Part part = make_part(blockIdx.x, warp_id, gridDim.x, A.wn, g.nx, true);
@@ -1105,7 +1131,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
                                                   bb + (size_t)i * P, Db + (size_t)i * P, exc);
             V4 nx, ny;
             flux_numerators(cur.pn, pc, pr, cur.cls, cls_c, cls_r, lane_id, inv_eps, have_exc, exc, nx, ny);
-            const V4 Ap = stencil_row<SAFE>(nx, ny, fxl, slow, h1, rh1, h2, rh2, mih1, mih2); // the expressions K1 used for (Ap,p)
+            const V4 Ap = stencil_row<SAFE>(nx, ny, fxl, slow, h1, rh1, h2, rh2, mih1, mih2, pow2); // the expressions K1 used for (Ap,p)
             V4 wn, rn;
 #pragma unroll
             for (int k = 0; k < LW; ++k) {

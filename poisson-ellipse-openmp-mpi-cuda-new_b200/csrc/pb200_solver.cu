@@ -75,6 +75,8 @@ Consts make_consts(const pb200_params &p) {
     c.h2 = (p.B2 - p.A2) / p.N; // S4:692
     c.rh1 = 1.0 / c.h1;
     c.rh2 = 1.0 / c.h2;
+    int e1 = 0, e2 = 0;
+    c.pow2 = (std::frexp(c.h1, &e1) == 0.5 ? 1 : 0) | (std::frexp(c.h2, &e2) == 0.5 ? 2 : 0);
     c.mih1 = -1.0 / c.h1; // S4:526
     c.mih2 = -1.0 / c.h2; // S4:530
     c.h1h1 = c.h1 * c.h1; // S4:556

@@ -99,6 +99,28 @@ def test_apply_A_bit_exact(oracle, nx, ny):
     assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("m,n,rect", [(64, 131, None), (128, 64, (-1.0, 1.0, -1.0, 1.0)), (50, 64, (-1.0, 1.0, -0.5, 0.5)),
+                                      (256, 512, (-2.0, 2.0, -1.0, 1.0))])
+def test_apply_A_power_of_two_steps(oracle, m, n, rect):
+    """A grid step that is a power of two (the 8192 and 32768 grids: h1 = 2/M) takes the kernel's one-multiplication
+    division path in x, in y or in both: still the reference's quotients, bit for bit."""
+    prm = pb.default_params(m, n)
+    if rect:
+        prm.A1, prm.B1, prm.A2, prm.B2 = rect
+    h1, h2 = (prm.B1 - prm.A1) / m, (prm.B2 - prm.A2) / n
+    nx, ny = m - 1, n - 1
+    a = np.abs(seeded_field(nx, ny, seed=1)) * 10 + 0.5
+    b = np.abs(seeded_field(nx, ny, seed=2)) * 10 + 0.5
+    a[3:9, :] = 1.0
+    b[3:9, :] = 1.0          # rows on the all-ones shortcut next to general ones
+    p = seeded_field(nx, ny, seed=3)
+    p[12:20, 5:40] *= 1e-290          # a patch that sends its rows to the IEEE-divide path
+    with np.errstate(under="ignore"):
+        want = oracle.apply_A(p, a, b, h1, h2)
+    got = pb.op_apply_A(prm, p, a, b)
+    assert np.array_equal(got, want)
+
+
 def test_apply_A_random_coefficients(oracle):
     nx, ny = 45, 130
     h1, h2 = steps(nx + 1, ny + 1)
@@ -160,7 +182,7 @@ def test_dot(oracle, golden, nx, ny):
 
 
 @pytest.mark.parametrize("nx,ny,first", [(39, 39, False), (39, 39, True), (1, 1, False), (9, 63, False),
-                                         (130, 67, False), (64, 1000, False)])
+                                         (130, 67, False), (64, 1000, False), (63, 200, False), (127, 127, True)])
 def test_fused_iteration(oracle, nx, ny, first):
     """One K1+K2 pass on caller data: every element-wise result bit-exact, scalars to RTOL_DOT."""
     m, n = nx + 1, ny + 1
