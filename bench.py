@@ -264,7 +264,7 @@ def main():
     # ---- roofline of the dominant kernel (N=1; per-kernel CUDA events inside the library)
     roofline = None
     if world == 1:
-        k1_ms, k2_ms = solver.profile_iteration(20)
+        k1_ms, k2_ms = solver.profile_iteration(int(os.environ.get("PB200_PROFILE_ITERS", "20")))
         peak, peak_src = measured_peak_gbs()
         dom, dom_ms, dom_bytes = ("k1_kernel", k1_ms, K1_BYTES) if k1_ms >= k2_ms else ("k2_kernel", k2_ms, K2_BYTES)
         achieved = pts * dom_bytes / (dom_ms * 1e-3) * 1e-9

@@ -670,27 +670,44 @@ __device__ __forceinline__ bool load_exceptions(const unsigned cls_a, const unsi
     return true;
 }
 
+// Rows of a warp window that lie wholly inside the ellipse (every class byte 0x00: a = b = 1, D = lutD[0]) or wholly
+// outside it (every byte 0x85: a = b = 1/eps, D = lutD[8]) are the bulk of the grid. One pair of warp reductions per
+// row (row_kind) recognises them, and the row step then skips the class decoding, the search for cut cells and the
+// per-cell table look-ups altogether.
+constexpr unsigned CLS_ROW_OUTSIDE = 0x85858585u;
+enum { ROW_GENERAL = 0, ROW_INSIDE = 1, ROW_OUTSIDE = 2 };
+
+struct ClsSummary {
+    unsigned any, all; // OR and AND of the class words of the warp's 32 lanes (warp-uniform)
+};
+__device__ __forceinline__ ClsSummary cls_summary(unsigned cls) {
+    ClsSummary s;
+    s.any = __reduce_or_sync(0xffffffffu, cls);
+    s.all = __reduce_and_sync(0xffffffffu, cls);
+    return s;
+}
+// kind of the row pair (i, i+1) a row step works on
+__device__ __forceinline__ int row_kind(const ClsSummary &c, const ClsSummary &n) {
+    const unsigned any = c.any | n.any, all = c.all & n.all;
+    return (any == 0u) ? ROW_INSIDE : ((all == CLS_ROW_OUTSIDE && any == CLS_ROW_OUTSIDE) ? ROW_OUTSIDE : ROW_GENERAL);
+}
+
 // The numerators of the eight face fluxes of a lane in one row, S4:527/531:
 //   nx[k] = a(i+1, c0+k) * (p(i+1, c0+k) - p(i, c0+k))          (x faces above the lane's cells)
 //   ny[k] = b(i, c0+k+1) * (p(i, c0+k+1) - p(i, c0+k))          (y faces right of the lane's cells)
-// a, b come from the class bytes: cls_n = classes of row i+1, cls_c = row i, cls_r = next lane's row i.
-// Rows that are wholly inside the ellipse (all classes 0: a = b = 1, the product with 1.0 is exact and skipped)
-// or wholly outside (all classes 1: a = b = 1/eps) take warp-uniform shortcuts.
+// a, b come from the class bytes: cls_n = classes of row i+1, cls_c = row i, cls_r = next lane's row i (general rows
+// only). Inside the ellipse a = b = 1: the product with 1.0 is exact and skipped.
 __device__ __forceinline__ void flux_numerators(const V4 &pn, const V4 &pc, const double pr, const unsigned cls_n,
                                                 const unsigned cls_c, const unsigned cls_r, const int lane,
-                                                const double inv_eps, const bool have_exc, const Exc &exc, V4 &nx,
-                                                V4 &ny) {
+                                                const double inv_eps, const int kind, const bool have_exc,
+                                                const Exc &exc, V4 &nx, V4 &ny) {
 #pragma unroll
     for (int k = 0; k < LW; ++k) nx.v[k] = pn.v[k] - pc.v[k];
 #pragma unroll
     for (int k = 0; k < LW - 1; ++k) ny.v[k] = pc.v[k + 1] - pc.v[k];
     ny.v[LW - 1] = pr - pc.v[LW - 1];
-    const unsigned ka = cls_n & 0x03030303u, kb = cls_c & 0x0c0c0c0cu;
-    const unsigned kr = ((lane < 31) ? cls_r : cls_c) & 0x0cu; // lane 31 has no right neighbour lane: its last face is unused
-    const bool all0 = (ka | kb | kr) == 0u;
-    const bool all1 = (ka == 0x01010101u) && (kb == 0x04040404u) && (kr == 0x04u);
-    if (__all_sync(0xffffffffu, all0)) return; // a = b = 1
-    if (__all_sync(0xffffffffu, all1)) {
+    if (kind == ROW_INSIDE) return; // a = b = 1
+    if (kind == ROW_OUTSIDE) {
 #pragma unroll
         for (int k = 0; k < LW; ++k) {
             nx.v[k] = inv_eps * nx.v[k];
@@ -737,12 +754,18 @@ __device__ __forceinline__ V4 xface_numerators(const V4 &pc, const V4 &pm, const
 // table read when the whole warp sits in one diagonal class, per-cell reads otherwise; cells next to the
 // ellipse boundary (general class) divide by the stored D, passed in D_exc.
 template <bool SAFE>
-__device__ __forceinline__ V4 precond4(const V4 &r, const unsigned cls, const double2 *s_lut, const V4 &D_exc) {
+__device__ __forceinline__ V4 precond4(const V4 &r, const unsigned cls, const double2 *s_lut, const V4 &D_exc,
+                                       const int kind = ROW_GENERAL) {
     V4 z;
-    const unsigned kd = (cls >> 4) & 0x0f0f0f0fu;
-    const unsigned k0 = __shfl_sync(0xffffffffu, kd, 0) & 0xfu;
     const bool slow = SAFE || __any_sync(0xffffffffu, range_bad4(r)); // a value outside the proven window: IEEE divides
-    if (__all_sync(0xffffffffu, kd == k0 * 0x01010101u) && k0 != DCLS_GENERAL) {
+    const unsigned kd = (cls >> 4) & 0x0f0f0f0fu;
+    unsigned k0 = (kind == ROW_INSIDE) ? 0u : 8u;
+    bool uniform = kind != ROW_GENERAL;
+    if (!uniform) {
+        k0 = __shfl_sync(0xffffffffu, kd, 0) & 0xfu;
+        uniform = __all_sync(0xffffffffu, kd == k0 * 0x01010101u) && k0 != DCLS_GENERAL;
+    }
+    if (uniform) {
         const double2 DR = s_lut[k0];
         if (slow) {
 #pragma unroll
@@ -897,8 +920,8 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         };
 #pragma unroll
         for (int t = 0; t < STAGES; ++t) issue((unsigned)(t * K1_STAGE_BYTES), 8u * t);
-        auto p_update = [&](const RowIn &in, const V4 &D_exc) {
-            V4 z = precond4<SAFE>(in.r, in.cls, s_lut, D_exc); // S4:559
+        auto p_update = [&](const RowIn &in, const V4 &D_exc, const int kind = ROW_GENERAL) {
+            V4 z = precond4<SAFE>(in.r, in.cls, s_lut, D_exc, kind); // S4:559
             if (!FIRST) {
 #pragma unroll
                 for (int k = 0; k < LW; ++k) z.v[k] = z.v[k] + beta * in.q.v[k]; // S4:675 (FIRST: p = z, S4:830)
@@ -917,6 +940,7 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
         load_exceptions(0u, 0u, 0u, in.cls, lane_id, ab, bb, Db + (size_t)L.i_lo * P, exc);
         V4 pc = p_update(in, exc.D);
         unsigned cls_c = in.cls;
+        ClsSummary sum_c = cls_summary(cls_c);
         st4_mask(po_row, pc, L.pw);
         bool bad_c = !SAFE && (range_bad4(pm) || range_bad4(pc));
         V4 fxl;
@@ -933,10 +957,17 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
 
         // one row: consumes the operands of row i+1, leaves p'(i+1), Fx(i+1/2) and the classes of row i+1
         auto row_step = [&](const int i, const RowIn &cur, const unsigned st_mask) {
-            const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
-            const bool have_exc = load_exceptions(cur.cls, cls_c, cls_r, cur.cls, lane_id, ab + (size_t)(i + 1) * P,
-                                                  bb + (size_t)i * P, Db + (size_t)(i + 1) * P, exc);
-            const V4 pn = p_update(cur, exc.D);
+            const ClsSummary sum_n = cls_summary(cur.cls);
+            const int kind = row_kind(sum_c, sum_n);
+            sum_c = sum_n;
+            unsigned cls_r = 0u;
+            bool have_exc = false;
+            if (kind == ROW_GENERAL) {
+                cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
+                have_exc = load_exceptions(cur.cls, cls_c, cls_r, cur.cls, lane_id, ab + (size_t)(i + 1) * P,
+                                           bb + (size_t)i * P, Db + (size_t)(i + 1) * P, exc);
+            }
+            const V4 pn = p_update(cur, exc.D, kind);
             po_row += P;
             st4_mask(po_row, pn, st_mask);
             const bool bad_n = !SAFE && range_bad4(pn);
@@ -944,7 +975,7 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
             bad_c = bad_n;
             const double pr = shfl_dn1(pc.v[0]); // right neighbour of the lane's last column
             V4 nx, ny;
-            flux_numerators(pn, pc, pr, cur.cls, cls_c, cls_r, lane_id, inv_eps, have_exc, exc, nx, ny);
+            flux_numerators(pn, pc, pr, cur.cls, cls_c, cls_r, lane_id, inv_eps, kind, have_exc, exc, nx, ny);
             const V4 out = stencil_row<SAFE>(nx, ny, fxl, slow, h1, rh1, h2, rh2, mih1, mih2, pow2);
             if (apb) st4_mask(apb + (size_t)i * P, out, L.own);
 #pragma unroll
@@ -1103,6 +1134,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
         const V4 pm = ldg4_nc(pb + (size_t)(L.i_lo - 1) * P, true);
         V4 pc = ldg4_nc(pb + (size_t)L.i_lo * P, true);
         unsigned cls_c = __ldg(reinterpret_cast<const unsigned *>(A.cls + cls_index(g.cpitch, L.i_lo, L.wcol, 4 * lane_id)));
+        ClsSummary sum_c = cls_summary(cls_c);
         bool bad_c = !SAFE && (range_bad4(pm) || range_bad4(pc));
         V4 fxl;
         {
@@ -1125,12 +1157,19 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
             const bool slow = __any_sync(0xffffffffu, bad_c | bad_n);
             bad_c = bad_n;
             const double pr = shfl_dn1(pc.v[0]);
-            const unsigned cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
+            const ClsSummary sum_n = cls_summary(cur.cls);
+            const int kind = row_kind(sum_c, sum_n);
+            sum_c = sum_n;
+            unsigned cls_r = 0u;
             Exc exc;
-            const bool have_exc = load_exceptions(cur.cls, cls_c, cls_r, cls_c, lane_id, ab + (size_t)(i + 1) * P,
-                                                  bb + (size_t)i * P, Db + (size_t)i * P, exc);
+            bool have_exc = false;
+            if (kind == ROW_GENERAL) {
+                cls_r = __shfl_down_sync(0xffffffffu, cls_c, 1);
+                have_exc = load_exceptions(cur.cls, cls_c, cls_r, cls_c, lane_id, ab + (size_t)(i + 1) * P, bb + (size_t)i * P,
+                                           Db + (size_t)i * P, exc);
+            }
             V4 nx, ny;
-            flux_numerators(cur.pn, pc, pr, cur.cls, cls_c, cls_r, lane_id, inv_eps, have_exc, exc, nx, ny);
+            flux_numerators(cur.pn, pc, pr, cur.cls, cls_c, cls_r, lane_id, inv_eps, kind, have_exc, exc, nx, ny);
             const V4 Ap = stencil_row<SAFE>(nx, ny, fxl, slow, h1, rh1, h2, rh2, mih1, mih2, pow2); // the expressions K1 used for (Ap,p)
             V4 wn, rn;
 #pragma unroll
@@ -1138,7 +1177,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
                 wn.v[k] = cur.w.v[k] + alpha * pc.v[k]; // S4:647
                 rn.v[k] = cur.r.v[k] - alpha * Ap.v[k]; // S4:648
             }
-            const V4 zn = precond4<SAFE>(rn, cls_c, s_lut, exc.D); // S4:559
+            const V4 zn = precond4<SAFE>(rn, cls_c, s_lut, exc.D, kind); // S4:559
 #pragma unroll
             for (int k = 0; k < LW; ++k) {
                 const bool own = (L.own >> k) & 1u;
