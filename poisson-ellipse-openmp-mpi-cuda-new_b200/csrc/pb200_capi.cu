@@ -28,6 +28,7 @@ struct OpBlock {
     cudaStream_t stream = nullptr;
     dim3 k1_grid, k2_grid, init_grid;
     int wn = 1;
+    Bands bands{1, 1, 0};
     bool safe_div = false;
 
     ~OpBlock() {
@@ -69,8 +70,12 @@ struct OpBlock {
         CK(cudaMalloc(&Ap, f.elems * sizeof(double)));
         for (double *q : {f.a, f.b, f.D, f.w, f.r, f.p[0], f.p[1], Ap}) CK(cudaMemset(q, 0, f.elems * sizeof(double)));
         wn = (ny + K1_OWN - 1) / K1_OWN;
-        // small pieces on purpose (3 rows per warp) so that the tests cross many piece and window boundaries
-        k1_grid = dim3(((nx + 2) / 3) * ((wn + K1_WARPS - 1) / K1_WARPS), 1, 1);
+        // small pieces on purpose, so that the tests cross many piece and window boundaries: 3-row bands over the first
+        // two thirds of the rows, 2-row bands over the rest
+        bands.nxA = nx >= 12 ? nx - nx / 3 : nx;
+        bands.nbA = (bands.nxA + 2) / 3;
+        bands.nbB = nx > bands.nxA ? (nx - bands.nxA + 1) / 2 : 0;
+        k1_grid = dim3((bands.nbA + bands.nbB) * ((wn + K1_WARPS - 1) / K1_WARPS), 1, 1);
         k2_grid = k1_grid;
         init_grid = dim3((ny + INIT_THREADS - 1) / INIT_THREADS, std::min(nx, 1024), 1);
         size_t nb = (size_t)k1_grid.x * k1_grid.y;
@@ -138,6 +143,7 @@ struct OpBlock {
         a.g = f.g;
         a.c = c;
         a.wn = wn;
+        a.bands = bands;
         if (first) {
             if (safe_div) k1_kernel<true, true><<<k1_grid, K1_THREADS, K1_SMEM>>>(a);
             else k1_kernel<true, false><<<k1_grid, K1_THREADS, K1_SMEM>>>(a);
@@ -162,6 +168,7 @@ struct OpBlock {
         a.g = f.g;
         a.c = c;
         a.wn = wn;
+        a.bands = bands;
         if (safe_div) k2_kernel<true><<<k2_grid, K2_THREADS, K2_SMEM>>>(a);
         else k2_kernel<false><<<k2_grid, K2_THREADS, K2_SMEM>>>(a);
         CK(cudaGetLastError());

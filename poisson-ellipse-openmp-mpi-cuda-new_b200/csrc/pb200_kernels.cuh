@@ -461,6 +461,11 @@ constexpr int K2_STAGE_BYTES = 3 * ROW_BYTES + CLS_WIN;     // p'(i+1), w(i), r(
 constexpr int K1_SMEM = K1_WARPS * STAGES * K1_STAGE_BYTES;
 constexpr int K2_SMEM = K1_WARPS * STAGES * K2_STAGE_BYTES;
 
+// How the rows are cut into bands (see Part below): nbA bands over rows 1..nxA, then nbB bands over the rest.
+struct Bands {
+    int nbA, nxA, nbB;
+};
+
 struct K1Args {
     const double *r, *p_old;
     const double *a, *b, *D; // full arrays, read only where the class says "general"
@@ -472,6 +477,7 @@ struct K1Args {
     Geom g;
     Consts c;
     int wn; // warp windows per row: ceil(ny / 124)
+    Bands bands;
     PeerView pv; // multi == 2
 };
 
@@ -486,6 +492,7 @@ struct K2Args {
     Geom g;
     Consts c;
     int wn;
+    Bands bands;
     PeerView pv; // multi == 2
 };
 
@@ -594,29 +601,35 @@ struct Lane {
     unsigned pw;   // bit k: column c0+k gets this lane's p' (owned interior cells + ring columns)
 };
 
-// Work partition. The rows are cut into NB = floor(warps / windows) bands of equal height (+-1 row) and warp gw
-// takes window gw % windows of band gw / windows: warps that run side by side read side-by-side windows of the same
-// rows (DRAM page locality). The host sizes the grid so that a band is about 20 rows (solver.cu: march_blocks).
+// Work partition. The rows are cut into bands -- nbA bands of equal height (+-1 row) over rows 1..nxA, then nbB lower
+// bands over the rest (Bands) -- and the 124-column warp windows into CTA-windows of K1_WARPS adjacent ones. CTA c takes
+// CTA-window c % wcn of band c / wcn, wcn = ceil(windows / K1_WARPS): warps that run side by side read side-by-side
+// windows of the same rows (DRAM page locality). CTAs start in index order, so the lower bands come last and keep the
+// end of the kernel -- when the SMs run out of CTAs one by one -- short. The host picks the bands (solver.cu:
+// march_plan). `descending`: the same bands counted from the last row upwards. K1 sweeps up the rows and K2 sweeps
+// back down, so each kernel starts on the ~100 MB the previous one touched last and finds them in the 126 MB L2.
 struct Part {
-    int nsub;                  // 0 or 1 sub-segments (kept as a list: the kernels loop over it)
+    int nsub;                  // 0 or 1 sub-segments
     int wcol[1], lo[1], hi[1]; // window and inclusive row range
-    int cta_rows;              // rows of the band this CTA works on (same for all its warps; 0 = none)
 };
 
-// CTA c takes CTA-window c % wcn (K1_WARPS adjacent warp windows) of band c / wcn, wcn = ceil(windows / K1_WARPS).
-// `descending`: bands are handed out from the last row upwards. K1 sweeps up the rows and K2 sweeps back down, so each
-// kernel starts on the ~100 MB the previous one touched last and finds them in the 126 MB L2 instead of in HBM.
-__device__ __forceinline__ Part make_part(int cta, int warp, int ncta, int wn, int nx, bool descending = false) {
+__device__ __forceinline__ Part make_part(int cta, int warp, int wn, int nx, const Bands &B, bool descending = false) {
     Part p;
     const int wcn = (wn + K1_WARPS - 1) / K1_WARPS;
-    const int nb = max(1, ncta / wcn);
-    const int bq = cta / wcn;
-    const int b = (descending && bq < nb) ? nb - 1 - bq : bq;
-    p.wcol[0] = (cta - bq * wcn) * K1_WARPS + warp;
-    p.lo[0] = 1 + (int)(((long long)nx * b) / nb);
-    p.hi[0] = (int)(((long long)nx * (b + 1)) / nb);
-    p.cta_rows = (b < nb && p.lo[0] <= p.hi[0]) ? p.hi[0] - p.lo[0] + 1 : 0;
-    p.nsub = (p.cta_rows > 0 && p.wcol[0] < wn) ? 1 : 0;
+    const int b = cta / wcn;
+    p.wcol[0] = (cta - b * wcn) * K1_WARPS + warp;
+    int lo = 1, hi = 0;
+    if (b < B.nbA) {
+        lo = 1 + (int)(((long long)B.nxA * b) / B.nbA);
+        hi = (int)(((long long)B.nxA * (b + 1)) / B.nbA);
+    } else if (b < B.nbA + B.nbB) {
+        const int k = b - B.nbA, nxB = nx - B.nxA;
+        lo = 1 + B.nxA + (int)(((long long)nxB * k) / B.nbB);
+        hi = B.nxA + (int)(((long long)nxB * (k + 1)) / B.nbB);
+    }
+    p.lo[0] = descending ? nx + 1 - hi : lo;
+    p.hi[0] = descending ? nx + 1 - lo : hi;
+    p.nsub = (lo <= hi && p.wcol[0] < wn) ? 1 : 0;
     return p;
 }
 
@@ -862,7 +875,7 @@ __global__ void __launch_bounds__(K1_THREADS, PB200_K1_MINB) k1_kernel(const K1A
     const double inv_eps = A.c.inv_eps;
     const int pow2 = A.c.pow2;
     const double beta = FIRST ? 0.0 : ctl->beta;
-    const Part part = make_part(blockIdx.x, warp_id, gridDim.x, A.wn, g.nx);
+    const Part part = make_part(blockIdx.x, warp_id, A.wn, g.nx, A.bands);
 
     double acc[1] = {0.0};
     if (part.nsub > 0) {
@@ -1071,11 +1084,7 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
     const double inv_eps = A.c.inv_eps;
     const int pow2 = A.c.pow2;
 
-#ifndef PB200_NO_REVERSE
-    const Part part = make_part(blockIdx.x, warp_id, gridDim.x, A.wn, g.nx, true);
-#else
-    const Part part = make_part(blockIdx.x, warp_id, gridDim.x, A.wn, g.nx);
-#endif
+    const Part part = make_part(blockIdx.x, warp_id, A.wn, g.nx, A.bands, true);
 
     double acc[2] = {0.0, 0.0};
     if (part.nsub > 0) {

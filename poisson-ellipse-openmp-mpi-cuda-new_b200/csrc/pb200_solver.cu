@@ -195,7 +195,7 @@ Solver::~Solver() {
 //   * the kernel lasts ceil(blocks / resident blocks) waves;
 //   * per-warp speed grows with the number of waves in flight behind each other (46 / 60 / 64.5 / 67 / 71 / 72.5
 //     G pt*it/s at 1 / 2 / 3 / 4 / 6 / 8 waves) -- many short pieces beat one resident wave.
-// PB200_ROWS overrides the choice (tuning).
+// PB200_ROWS overrides the choice (tuning). The plan also carries the lower bands that end the sweep (below).
 static double wave_gain(double w) {
     static const double x[] = {0.0, 0.5, 1.0, 2.0, 3.0, 4.0, 6.0, 8.0}, y[] = {0.0, 0.42, 0.63, 0.83, 0.89, 0.925, 0.98, 1.0};
     if (w >= 8.0) return 1.0;
@@ -204,23 +204,44 @@ static double wave_gain(double w) {
     return 1.0;
 }
 
-int march_blocks(int resident_blocks, int wn, int nx) {
+MarchPlan march_plan(int resident_blocks, int wn, int nx) {
+    const int wcn = (wn + K1_WARPS - 1) / K1_WARPS;
     auto blocks_for = [&](int rows) { // bands x CTA-windows (make_part)
-        return ((nx + rows - 1) / rows) * ((wn + K1_WARPS - 1) / K1_WARPS);
+        return ((nx + rows - 1) / rows) * wcn;
     };
-    if (const char *e = std::getenv("PB200_ROWS")) return blocks_for(std::max(1, atoi(e)));
     const double resident = std::max(1, resident_blocks);
     int best_rows = 20;
-    double best_cost = 1e300;
-    for (int rows = 2; rows <= 24; ++rows) {
-        const double waves = blocks_for(rows) / resident;
-        const double cost = std::ceil(waves) * (rows + 2) / wave_gain(waves);
-        if (cost < best_cost * 0.999) {
-            best_cost = cost;
-            best_rows = rows;
+    if (const char *e = std::getenv("PB200_ROWS")) best_rows = std::min(nx, std::max(1, atoi(e)));
+    else {
+        double best_cost = 1e300;
+        for (int rows = 2; rows <= 24; ++rows) {
+            const double waves = blocks_for(rows) / resident;
+            const double cost = std::ceil(waves) * (rows + 2) / wave_gain(waves);
+            if (cost < best_cost * 0.999) {
+                best_cost = cost;
+                best_rows = rows;
+            }
         }
     }
-    return blocks_for(best_rows);
+    // Tail: when the kernel is many waves long, the last wave and a half of CTAs get bands half as high
+    // (measured at 8192^2: 78.0 G pt*it/s without, 80.6 with; a third or a sixth as high gains less), so that the
+    // SMs run dry within a few row steps of each other instead of within a whole band (PB200_TAIL=0: off).
+    MarchPlan m{};
+    int tail_rows = std::max(2, best_rows / 2), nxB = 0;
+    double tail_waves = 1.5;
+    if (const char *e = std::getenv("PB200_TAIL_WAVES")) tail_waves = std::max(0.1, atof(e));
+    if (const char *e = std::getenv("PB200_TAIL_ROWS")) tail_rows = std::max(1, atoi(e));
+    bool tail = best_rows >= 9 && blocks_for(best_rows) / resident >= 4.0;
+    if (const char *e = std::getenv("PB200_TAIL")) tail = tail && atoi(e) != 0;
+    if (tail) {
+        const long long tail_bands = (long long)std::ceil(tail_waves * resident / wcn);
+        nxB = (int)std::min<long long>(nx / 5, tail_bands * tail_rows);
+    }
+    m.bands.nxA = nx - nxB;
+    m.bands.nbA = (m.bands.nxA + best_rows - 1) / best_rows;
+    m.bands.nbB = nxB > 0 ? (nxB + tail_rows - 1) / tail_rows : 0;
+    m.ctas = (m.bands.nbA + m.bands.nbB) * wcn;
+    return m;
 }
 
 void Solver::plan_launch() {
@@ -229,8 +250,10 @@ void Solver::plan_launch() {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ1, k1_kernel<false, false>, K1_THREADS, K1_SMEM);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ2, k2_kernel<false>, K2_THREADS, K2_SMEM);
-    k1_grid = dim3(march_blocks(std::max(1, occ1) * sms, wn, f.g.nx), 1, 1);
-    k2_grid = dim3(march_blocks(std::max(1, occ2) * sms, wn, f.g.nx), 1, 1);
+    k1_plan = march_plan(std::max(1, occ1) * sms, wn, f.g.nx);
+    k2_plan = march_plan(std::max(1, occ2) * sms, wn, f.g.nx);
+    k1_grid = dim3(k1_plan.ctas, 1, 1);
+    k2_grid = dim3(k2_plan.ctas, 1, 1);
     norms_grid = dim3((f.g.ny + 255) / 256, std::min(f.g.nx, 512), 1);
     init_grid = dim3((f.g.ny + INIT_THREADS - 1) / INIT_THREADS, std::min(f.g.nx, 1024), 1);
 }
@@ -319,6 +342,7 @@ K1Args Solver::k1_args(long long k) const {
     a.g = f.g;
     a.c = c;
     a.wn = wn;
+    a.bands = k1_plan.bands;
     a.pv = pv;
     return a;
 }
@@ -338,6 +362,7 @@ K2Args Solver::k2_args(long long k) const {
     a.g = f.g;
     a.c = c;
     a.wn = wn;
+    a.bands = k2_plan.bands;
     a.pv = pv;
     return a;
 }

@@ -27,7 +27,11 @@ bool coef_in_div_range(double v); // zero, or 2^-50 <= |v| <= 2^300
 int pitch_for(int ny);
 int cpitch_for(int ny);
 pb200_status enable_kernel_smem();
-int march_blocks(int resident_blocks, int wn, int nx);
+struct MarchPlan {
+    int ctas;    // grid size: (bands.nbA + bands.nbB) x CTA-windows
+    Bands bands; // how the rows are cut
+};
+MarchPlan march_plan(int resident_blocks, int wn, int nx);
 
 // The device arrays of one block. Hot (touched every iteration): w, r, p[0], p[1] (ping-pong) and one class
 // byte per cell. Cold (written once by setup, read only on cells cut by the ellipse): a, b, D.
@@ -60,6 +64,7 @@ struct Solver {
     dim3 k1_grid, k2_grid, norms_grid, init_grid;
     bool safe_div = false; // coefficients outside div_const's verified range: IEEE divides everywhere
     int wn = 1; // warp windows per row
+    MarchPlan k1_plan{}, k2_plan{};
     long long launches = 0;
     long long last_iter = 0;
     double t_setup = 0.0;
