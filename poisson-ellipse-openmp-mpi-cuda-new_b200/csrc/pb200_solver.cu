@@ -223,15 +223,17 @@ MarchPlan march_plan(int resident_blocks, int wn, int nx) {
             }
         }
     }
-    // Tail: when the kernel is many waves long, the last wave and a half of CTAs get bands half as high
-    // (measured at 8192^2: 78.0 G pt*it/s without, 80.6 with; a third or a sixth as high gains less), so that the
-    // SMs run dry within a few row steps of each other instead of within a whole band (PB200_TAIL=0: off).
+    // Tail: the last CTAs to start get bands half as high, so that the SMs run dry within a few row steps of each other
+    // instead of within a whole band: the last wave and a half of a long kernel, three quarters of a wave of a short one.
+    // Measured: 8192^2 78.0 -> 80.7 G pt*it/s, 4096^2 291 -> 270 us, 2400x3200 166 -> 159 us per iteration; bands a third
+    // or a sixth as high gain less. PB200_TAIL=0 switches it off, PB200_TAIL_ROWS / PB200_TAIL_WAVES override (tuning).
     MarchPlan m{};
+    const double waves = blocks_for(best_rows) / resident;
     int tail_rows = std::max(2, best_rows / 2), nxB = 0;
-    double tail_waves = 1.5;
+    double tail_waves = waves >= 4.0 ? 1.5 : 0.75;
     if (const char *e = std::getenv("PB200_TAIL_WAVES")) tail_waves = std::max(0.1, atof(e));
     if (const char *e = std::getenv("PB200_TAIL_ROWS")) tail_rows = std::max(1, atoi(e));
-    bool tail = best_rows >= 9 && blocks_for(best_rows) / resident >= 4.0;
+    bool tail = best_rows >= 4 && waves >= 1.0;
     if (const char *e = std::getenv("PB200_TAIL")) tail = tail && atoi(e) != 0;
     if (tail) {
         const long long tail_bands = (long long)std::ceil(tail_waves * resident / wcn);
