@@ -110,6 +110,14 @@ pb200_status pb200_choose_process_grid(int32_t size, int32_t *Px, int32_t *Py);
 pb200_status pb200_decompose_2d(int32_t M, int32_t N, int32_t Px, int32_t Py, int32_t rank, int32_t *i_start,
                                 int32_t *i_end, int32_t *j_start, int32_t *j_end);
 
+/* Host-only introspection, no reference counterpart: how the two iteration kernels would cut a block of nx x ny
+ * interior cells into work when `resident_ctas` of their CTAs fit on the GPU at once (592 on a B200: 148 SMs x 4).
+ * plan[0] = bands of the main part, plan[1] = rows the main part covers (1..plan[1]), plan[2] = lower bands over the
+ * remaining rows, plan[3] = CTAs launched, plan[4] = 124-column warp windows per row, plan[5] = warps per CTA.
+ * Band b < plan[0] holds rows 1 + plan[1]*b/plan[0] .. plan[1]*(b+1)/plan[0] (integer division), the lower bands
+ * split the rest the same way. Needs no GPU; used by the CPU tests to check that every row is covered once. */
+pb200_status pb200_launch_plan(int32_t nx, int32_t ny, int32_t resident_ctas, int32_t plan[6]);
+
 /* ---- the solver (replaces gradient_solver_mpi, S4:688-983) ---------------------------- */
 /* Allocates the block on the device and runs the coefficient/RHS kernel
  * (replaces fictitious_regions_setup_local S4:146-192 + flatten/upload S4:723-760). */

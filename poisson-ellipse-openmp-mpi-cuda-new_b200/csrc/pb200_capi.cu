@@ -239,6 +239,22 @@ pb200_status pb200_choose_process_grid(int32_t size, int32_t *Px, int32_t *Py) {
     return PB200_OK;
 }
 
+pb200_status pb200_launch_plan(int32_t nx, int32_t ny, int32_t resident_ctas, int32_t plan[6]) {
+    if (nx < 1 || ny < 1 || resident_ctas < 1 || !plan) {
+        set_error("bad arguments");
+        return PB200_ERR_INVALID;
+    }
+    const int wn = (ny + K1_OWN - 1) / K1_OWN;
+    const MarchPlan m = march_plan(resident_ctas, wn, nx);
+    plan[0] = m.bands.nbA;
+    plan[1] = m.bands.nxA;
+    plan[2] = m.bands.nbB;
+    plan[3] = m.ctas;
+    plan[4] = wn;
+    plan[5] = K1_WARPS;
+    return PB200_OK;
+}
+
 pb200_status pb200_decompose_2d(int32_t M, int32_t N, int32_t Px, int32_t Py, int32_t rank, int32_t *i_start,
                                 int32_t *i_end, int32_t *j_start, int32_t *j_end) {
     if (M < 2 || N < 2 || Px < 1 || Py < 1 || rank < 0 || rank >= Px * Py || !i_start || !i_end || !j_start || !j_end) {

@@ -38,11 +38,44 @@ def test_process_grid_and_decomposition(golden):
         assert [list(pb.decompose_2d(m, n, px, py, r)) for r in range(int(p))] == blocks, key
 
 
+def bands_of(nx, plan):
+    """Row ranges of the bands a launch plan describes (the arithmetic of make_part in pb200_kernels.cuh)."""
+    nbA, nxA, nbB = plan[:3]
+    out = [(1 + nxA * b // nbA, nxA * (b + 1) // nbA) for b in range(nbA)]
+    out += [(1 + nxA + (nx - nxA) * k // nbB, nxA + (nx - nxA) * (k + 1) // nbB) for k in range(nbB)]
+    return out
+
+
+def test_launch_plan_covers_every_row_exactly_once():
+    """The bands of the two iteration kernels must tile rows 1..nx without gap or overlap, whatever the block size:
+    a row left out would silently keep its old values (the GPU parity tests only see the sizes they run)."""
+    import random
+    rnd = random.Random(7)
+    cases = [(nx, ny) for nx in (1, 2, 3, 4, 5, 7, 8, 9, 11, 12, 13, 23, 24, 25, 39, 47, 48, 49, 399, 799, 2399, 4095,
+                                 8191, 16383, 32767) for ny in (1, 39, 124, 125, 599, 3199, 8191, 32767)]
+    cases += [(rnd.randint(1, 40000), rnd.randint(1, 40000)) for _ in range(300)]
+    for resident in (592, 148, 1, 7):
+        for nx, ny in cases:
+            plan = pb.launch_plan(nx, ny, resident)
+            nbA, nxA, nbB, ctas, wn, warps = plan
+            assert wn == -(-ny // 124) and warps >= 1
+            assert nbA >= 1 and 1 <= nxA <= nx and nbB >= 0 and (nbB > 0) == (nxA < nx), (nx, ny, plan)
+            assert ctas == (nbA + nbB) * -(-wn // warps), (nx, ny, plan)
+            bands = bands_of(nx, plan)
+            assert bands[0][0] == 1 and bands[-1][1] == nx, (nx, ny, plan)
+            for (lo, hi), (lo2, _) in zip(bands, bands[1:] + [(nx + 1, 0)]):
+                assert lo <= hi and lo2 == hi + 1, (nx, ny, plan, lo, hi, lo2)
+            if nbB:          # the tail bands are the lower ones and cover at most a fifth of the rows
+                assert nx - nxA <= nx // 5 and (nx - nxA) / nbB <= nxA / nbA + 1, (nx, ny, plan)
+
+
 def test_bad_arguments_are_rejected():
     with pytest.raises(pb.PB200Error):
         pb.decompose_2d(40, 40, 2, 2, 4)
     with pytest.raises(pb.PB200Error):
         pb.choose_process_grid(0)
+    with pytest.raises(pb.PB200Error):
+        pb.launch_plan(0, 40)
     with pytest.raises(pb.PB200Error, match="M and N"):
         pb.run(pb.default_params(1, 40))
 
