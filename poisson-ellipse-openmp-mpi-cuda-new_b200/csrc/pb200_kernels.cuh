@@ -16,6 +16,7 @@
 // element (li,lj) at base[li*pitch + lj]; pitch is a multiple of 16 doubles so every row starts on
 // a 128-byte line; columns ny+2..pitch-1 are padding.
 #pragma once
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -1233,6 +1234,194 @@ __global__ void __launch_bounds__(K2_THREADS, PB200_K2_MINB) k2_kernel(const K2A
                 ctl->done = 1;
             }
         }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// The whole PCG loop (S4:845-943) of a SMALL single-GPU block in one cooperative launch, one thread per cell.
+//
+// The marching kernels above are built for throughput: a warp walks down its rows, a row step is a dependent sequence of
+// some 400 instructions (about 1.6 us for a warp that runs alone), and two dependent kernels per iteration each spend
+// about 14 us on launch gap, control-block loads, fence + ticket and the last block's pass. On a block of a few hundred
+// rows nothing hides any of that: an iteration costs 27-35 us whatever the size (measured; per-cell kernels in the same
+// two-launch scheme: no better). Here every cell has a resident thread that keeps its w, r, p and Ap in registers for
+// the whole solve, the two reductions of an iteration are a block sum, one grid-wide barrier and a pass over the block
+// partials that EVERY block makes for itself (same values, same order: bit-identical scalars in all threads, so the
+// stop decision needs no broadcast), and nothing goes through the control block until the end.
+//
+// Arithmetic: term by term that of the marching kernels -- p' = r/D + beta p on the cell and its four neighbours
+// (S4:559, 675), the four face fluxes and the stencil (S4:526-535) with IEEE divisions (which the constant-divisor
+// scheme there reproduces), the updates (S4:640-656) -- so p', w, r are bit-identical to the two-kernel path given the
+// same scalars; only the grouping of the partial sums differs. Coefficients come from the full a, b, D arrays.
+// Neighbours' r and p are read from global memory past L1 (__ldcg): they were written by other SMs in this launch.
+constexpr int CL_BX = 64, CL_BY = 4, CL_THREADS = CL_BX * CL_BY;
+
+struct CellLoopArgs {
+    double *w, *r, *p[2];
+    const double *a, *b, *D;
+    double *partials; // [3][blocks]: (Ap,p) | dw^2 | (z,r)
+    double *trace;
+    Ctl *ctl;
+    Geom g;
+    Consts c;
+};
+
+// Sum of v over the block, the same value in every thread: fixed warp tree, then the warps in index order.
+template <int NV>
+__device__ __forceinline__ void block_sum_all(double (&v)[NV], double (*s_w)[CL_THREADS / 32]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads(); // s_w may still be read from the previous use
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        const double w = warp_sum(v[k]);
+        if (lane == 0) s_w[k][warp] = w;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < CL_THREADS / 32; ++w) s += s_w[k][w];
+        v[k] = s;
+    }
+}
+
+// Grid-wide sums: every block leaves its partial, the grid meets, every block adds all partials up in index order.
+template <int NV>
+__device__ __forceinline__ void grid_sum_all(double (&v)[NV], double *partials, const unsigned nblocks, const unsigned bid,
+                                             double (*s_w)[CL_THREADS / 32], cooperative_groups::grid_group &grid) {
+    block_sum_all<NV>(v, s_w);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) __stcg(&partials[(size_t)k * nblocks + bid], v[k]);
+    }
+    grid.sync();
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+        double s = 0.0;
+        for (unsigned i = threadIdx.x; i < nblocks; i += CL_THREADS) s += __ldcg(&partials[(size_t)k * nblocks + i]);
+        v[k] = s;
+    }
+    block_sum_all<NV>(v, s_w);
+}
+
+// NC cells per thread (rows li, li + CL_BY, ...): their w, r, p and Ap stay in registers, coefficients and divisors are
+// re-read every iteration through the read-only path (they sit in L1). The host picks the smallest NC for which the
+// grid is resident (solver.cu: plan_launch).
+template <int NC>
+__global__ void __launch_bounds__(CL_THREADS, NC <= 2 ? 4 : 3) cell_loop_kernel(const CellLoopArgs A) {
+    __shared__ double s_w[2][CL_THREADS / 32];
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    const Geom g = A.g;
+    const Consts &c = A.c;
+    const unsigned nblocks = gridDim.x * gridDim.y, bid = blockIdx.y * gridDim.x + blockIdx.x;
+    const int lj = 1 + (int)blockIdx.x * CL_BX + (int)(threadIdx.x % CL_BX);
+    const int li0 = 1 + (int)blockIdx.y * (CL_BY * NC) + (int)(threadIdx.x / CL_BX);
+    const size_t P = (size_t)g.pitch;
+    bool own[NC];
+    size_t o[NC];
+    double w[NC], r[NC], pc[NC], Ap[NC];
+#pragma unroll
+    for (int q = 0; q < NC; ++q) {
+        const int li = li0 + q * CL_BY;
+        own[q] = li <= g.nx && lj <= g.ny;
+        o[q] = own[q] ? (size_t)li * P + lj : P + 1; // idle slots look at cell (1,1), harmlessly, and store nothing
+        w[q] = A.w[o[q]]; // S4:805-813: w = 0, r = B, p = 0 (setup_kernel / reset_kernel)
+        r[q] = A.r[o[q]];
+        pc[q] = 0.0;
+        Ap[q] = 0.0;
+    }
+    double zr_old = __ldcg(&A.ctl->zr_old); // init_kernel (S4:820-843)
+    double alpha = 0.0, beta = 0.0, diff = 0.0, denom = 0.0;
+    long long k = 0;
+    int status = STOP_MAX_ITER, conv_iter = 0;
+    for (;;) {
+        ++k; // S4:847-848
+        const double *p_old = A.p[(k - 1) & 1];
+        double *p_new = A.p[k & 1];
+        const bool first = k == 1;
+        // ---- K1: p' on the cell and its neighbours, Ap, (Ap, p')
+        double s1[1] = {0.0};
+#pragma unroll
+        for (int q = 0; q < NC; ++q) {
+            const size_t oc = o[q];
+            const double zl = precond_div(__ldcg(&A.r[oc - 1]), __ldg(&A.D[oc - 1]));
+            const double zrr = precond_div(__ldcg(&A.r[oc + 1]), __ldg(&A.D[oc + 1]));
+            const double zd = precond_div(__ldcg(&A.r[oc - P]), __ldg(&A.D[oc - P]));
+            const double zu = precond_div(__ldcg(&A.r[oc + P]), __ldg(&A.D[oc + P]));
+            const double zc = precond_div(r[q], __ldg(&A.D[oc])); // S4:559
+            const double pl = first ? zl : zl + beta * __ldcg(&p_old[oc - 1]);
+            const double pr = first ? zrr : zrr + beta * __ldcg(&p_old[oc + 1]);
+            const double pd = first ? zd : zd + beta * __ldcg(&p_old[oc - P]);
+            const double pu = first ? zu : zu + beta * __ldcg(&p_old[oc + P]);
+            const double pq = first ? zc : zc + beta * pc[q]; // S4:675 (first: p = z, S4:830)
+            pc[q] = pq;
+            if (own[q]) __stcg(&p_new[oc], pq);
+            const double fx_hi = __ddiv_rn(__ldg(&A.a[oc + P]) * (pu - pq), c.h1), fx_lo = __ddiv_rn(__ldg(&A.a[oc]) * (pq - pd), c.h1); // S4:527
+            const double fy_hi = __ddiv_rn(__ldg(&A.b[oc + 1]) * (pr - pq), c.h2), fy_lo = __ddiv_rn(__ldg(&A.b[oc]) * (pq - pl), c.h2); // S4:531
+            Ap[q] = c.mih1 * (fx_hi - fx_lo) + c.mih2 * (fy_hi - fy_lo); // S4:526-535
+            s1[0] += own[q] ? Ap[q] * pq : 0.0;                          // S4:594
+        }
+        grid_sum_all<1>(s1, A.partials, nblocks, bid, s_w, grid);
+        denom = s1[0] * c.h1 * c.h2; // S3:191
+        const bool brk = (c.norm_mode == 1) ? (denom < 1e-15) : (fabs(denom) < 1e-15); // S0:128 | S4:876
+        if (brk) {
+            status = STOP_DENOM;
+            break;
+        }
+        // ---- K2: the updates and the two sums
+        alpha = zr_old / denom; // S4:877
+        double s2[2] = {0.0, 0.0};
+#pragma unroll
+        for (int q = 0; q < NC; ++q) {
+            const double wn = w[q] + alpha * pc[q]; // S4:647
+            const double rn = r[q] - alpha * Ap[q]; // S4:648
+            const double d = wn - w[q];             // S4:653
+            w[q] = wn;
+            r[q] = rn;
+            if (own[q]) __stcg(&A.r[o[q]], rn); // the neighbours' next p' needs it
+            s2[0] += own[q] ? d * d : 0.0;
+            s2[1] += own[q] ? precond_div(rn, __ldg(&A.D[o[q]])) * rn : 0.0; // S4:559, 594
+        }
+        grid_sum_all<2>(s2, A.partials + nblocks, nblocks, bid, s_w, grid);
+        // ---- the scalar tail (finalize_iteration), in every thread
+        const double zr_new = s2[1] * c.h1 * c.h2;
+        diff = (c.norm_mode == 0) ? sqrt(s2[0] * c.h1 * c.h2) : sqrt(s2[0]); // S3:449 | S0:154
+        const bool conv = diff < c.delta;                                     // S4:899
+        const bool tr = A.trace && k <= c.trace_len && bid == 0 && threadIdx.x == 0;
+        if (tr) {
+            A.trace[3 * (k - 1) + 0] = alpha;
+            A.trace[3 * (k - 1) + 1] = 0.0;
+            A.trace[3 * (k - 1) + 2] = diff;
+        }
+        if (conv && conv_iter == 0) conv_iter = (int)k;
+        if (conv && !c.fixed) {
+            status = STOP_CONVERGED;
+            break;
+        }
+        beta = zr_new / zr_old; // S4:931
+        zr_old = zr_new;        // S4:932
+        if (tr) A.trace[3 * (k - 1) + 1] = beta;
+        if (k >= c.max_iter) { // S4:847: loop bound
+            status = STOP_MAX_ITER;
+            break;
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < NC; ++q)
+        if (own[q]) A.w[o[q]] = w[q];
+    if (bid == 0 && threadIdx.x == 0) {
+        Ctl *ctl = A.ctl;
+        ctl->zr_old = zr_old;
+        ctl->denom = denom;
+        ctl->alpha = alpha;
+        ctl->beta = beta;
+        ctl->diff = diff;
+        ctl->iter = k;
+        ctl->status = status;
+        ctl->conv_iter = conv_iter;
+        __threadfence();
+        ctl->done = 1;
     }
 }
 

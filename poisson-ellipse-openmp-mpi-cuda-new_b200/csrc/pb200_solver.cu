@@ -256,6 +256,27 @@ void Solver::plan_launch() {
     k2_plan = march_plan(std::max(1, occ2) * sms, wn, f.g.nx);
     k1_grid = dim3(k1_plan.ctas, 1, 1);
     k2_grid = dim3(k2_plan.ctas, 1, 1);
+    // Small single-GPU blocks: the whole loop as one cooperative launch with a resident thread per cell (cell_loop_kernel),
+    // if the GPU can hold a thread for every cell at once. PB200_LOOP=0 switches it off (tuning, tests).
+    use_loop = false;
+    int coop = 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    const char *env_loop = std::getenv("PB200_LOOP");
+    if (c.multi == 0 && coop && !(env_loop && atoi(env_loop) == 0)) {
+        for (int nc : {1, 2, 4}) { // cells per thread: the smallest for which every block is resident
+            int occL = 0;
+            if (nc == 1) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occL, cell_loop_kernel<1>, CL_THREADS, 0);
+            if (nc == 2) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occL, cell_loop_kernel<2>, CL_THREADS, 0);
+            if (nc == 4) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occL, cell_loop_kernel<4>, CL_THREADS, 0);
+            const dim3 grid((f.g.ny + CL_BX - 1) / CL_BX, (f.g.nx + CL_BY * nc - 1) / (CL_BY * nc), 1);
+            if (static_cast<long long>(grid.x) * grid.y <= static_cast<long long>(occL) * sms) {
+                use_loop = true;
+                loop_cells = nc;
+                loop_grid = grid;
+                break;
+            }
+        }
+    }
     norms_grid = dim3((f.g.ny + 255) / 256, std::min(f.g.nx, 512), 1);
     init_grid = dim3((f.g.ny + INIT_THREADS - 1) / INIT_THREADS, std::min(f.g.nx, 1024), 1);
 }
@@ -296,7 +317,8 @@ pb200_status Solver::create(const pb200_params &params) {
     st = f.allocate(g);
     if (st != PB200_OK) return st;
     plan_launch();
-    const size_t nb1 = static_cast<size_t>(k1_grid.x) * k1_grid.y, nb2 = static_cast<size_t>(k2_grid.x) * k2_grid.y;
+    const size_t nbL = use_loop ? static_cast<size_t>(loop_grid.x) * loop_grid.y : 0; // cell_loop_kernel: 3 partials per block
+    const size_t nb1 = static_cast<size_t>(k1_grid.x) * k1_grid.y, nb2 = std::max(static_cast<size_t>(k2_grid.x) * k2_grid.y, (3 * nbL + 1) / 2);
     CK(cudaMalloc(&ctl, sizeof(Ctl)));
     CK(cudaMalloc(&part1, nb1 * sizeof(double)));
     const size_t nb3 = std::max(static_cast<size_t>(norms_grid.x) * norms_grid.y, static_cast<size_t>(init_grid.x) * init_grid.y);
@@ -446,11 +468,34 @@ pb200_status Solver::solve(pb200_result *res) {
     const bool use_graph = prm.use_graph != 0 && c.multi != 1;
     CK(cudaEventRecord(ev_start, stream));
     long long k = 1;
-    launch_iteration(k, true); // iteration 1: p = z (S4:830)
-    launches += kernels_per_iteration();
-    ++k;
+    if (use_loop) { // one cooperative launch runs every iteration; delta and max_iter are enforced on the device
+        CellLoopArgs la{};
+        la.w = f.w;
+        la.r = f.r;
+        la.p[0] = f.p[0];
+        la.p[1] = f.p[1];
+        la.a = f.a;
+        la.b = f.b;
+        la.D = f.D;
+        la.partials = part2;
+        la.trace = trace;
+        la.ctl = ctl;
+        la.g = f.g;
+        la.c = c;
+        void *args[] = {&la};
+        const void *fn = loop_cells == 1   ? reinterpret_cast<const void *>(cell_loop_kernel<1>)
+                         : loop_cells == 2 ? reinterpret_cast<const void *>(cell_loop_kernel<2>)
+                                           : reinterpret_cast<const void *>(cell_loop_kernel<4>);
+        CK(cudaLaunchCooperativeKernel(fn, loop_grid, dim3(CL_THREADS, 1, 1), args, 0, stream));
+        ++launches;
+        k = c.max_iter + 1;
+    } else {
+        launch_iteration(k, true); // iteration 1: p = z (S4:830)
+        launches += kernels_per_iteration();
+        ++k;
+    }
     CK(cudaGetLastError());
-    if (use_graph && !graph_exec && c.max_iter > 1) {
+    if (!use_loop && use_graph && !graph_exec && c.max_iter > 1) {
         cudaGraph_t graph = nullptr;
         CK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
         launch_iteration(2, false);

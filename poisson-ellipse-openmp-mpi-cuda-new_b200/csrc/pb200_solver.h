@@ -65,6 +65,9 @@ struct Solver {
     bool safe_div = false; // coefficients outside div_const's verified range: IEEE divides everywhere
     int wn = 1; // warp windows per row
     MarchPlan k1_plan{}, k2_plan{};
+    bool use_loop = false; // small block: the whole loop is one cooperative launch (cell_loop_kernel)
+    dim3 loop_grid;
+    int loop_cells = 1; // cells per thread of cell_loop_kernel
     long long launches = 0;
     long long last_iter = 0;
     double t_setup = 0.0;

@@ -26,6 +26,15 @@ def steps(m, n):
     return 2.0 / m, 1.2 / n
 
 
+def fetch_field(ptr, pitch, nx, ny):
+    """Host copy of a device block in the solver's layout (rows 0..nx+1 of `pitch` doubles), columns 0..ny+1."""
+    from cuda.bindings import runtime as rt
+    host = np.empty((nx + 2, pitch))
+    err, = rt.cudaMemcpy(host.ctypes.data, ptr, host.nbytes, rt.cudaMemcpyKind.cudaMemcpyDeviceToHost)
+    assert int(err) == 0, err
+    return host[:, :ny + 2].copy()
+
+
 # --------------------------------------------------------------------------------------------
 # division by a grid-uniform constant (used four times per point by the stencil)
 
@@ -269,7 +278,51 @@ def test_solve_800x1200(oracle, golden):
     assert rel(res.w_max, g["w_max"]) < 5e-9
 
 
-def test_graph_and_plain_launches_agree_bitwise():
+@pytest.mark.parametrize("m,n,kw", [(10, 10, {}), (40, 40, {}), (120, 90, {}), (400, 600, {}), (37, 53, {"norm_mode": 1}),
+                                    (100, 140, {"fixed_iters": 75}), (64, 64, {"max_iter": 9}), (65, 300, {"eps": 1e-3}),
+                                    (500, 640, {}), (2, 2, {}), (3, 130, {})])
+def test_resident_loop_and_two_kernel_paths_agree(monkeypatch, m, n, kw):
+    """Small single-GPU blocks run the whole loop as one cooperative launch with a resident thread per cell
+    (cell_loop_kernel: 1, 2 or 4 cells per thread); PB200_LOOP=0 forces the two marching kernels. Element-wise arithmetic
+    is the same term by term, the grouping of the partial sums is not: iteration counts are equal, the per-iteration
+    scalars agree to 1e-10, the solution to 1e-12 (the same bar as between GPU counts)."""
+    if "norm_mode" in kw:
+        kw = dict(kw, norm_mode=pb.NORM_STAGE0)
+    outs = []
+    for mode in ("0", "1"):
+        monkeypatch.setenv("PB200_LOOP", mode)
+        with pb.Solver(pb.default_params(m, n, trace_len=8, **kw)) as s:
+            res = s.solve()
+            res2 = s.solve()          # and again on the same handle
+            assert res2.iterations == res.iterations and res2.zr == res.zr
+            outs.append((res, s.solution(), s.trace(8), res.kernel_launches))
+    (r0, w0, t0, l0), (r1, w1, t1, l1) = outs
+    assert l1 <= 4 and (l0 > l1 or r0.iterations < 2)          # the loop path is one launch (+ reset, init, norms)
+    assert r0.iterations == r1.iterations and r0.stop_reason == r1.stop_reason
+    assert r0.first_converged_iter == r1.first_converged_iter
+    assert rel(r0.diff_norm, r1.diff_norm) < 1e-9 and rel(r0.w_norm_E, r1.w_norm_E) < RTOL_NORM and rel(r0.zr, r1.zr) < 1e-9
+    assert rel(r0.alpha, r1.alpha) < 1e-9 and rel(r0.beta, r1.beta) < 1e-9
+    np.testing.assert_allclose(t0, t1, rtol=1e-10, atol=0)
+    np.testing.assert_allclose(w0, w1, rtol=0, atol=1e-12)
+
+
+def test_resident_loop_first_iteration_bitwise(monkeypatch):
+    """After ONE iteration p' (stored by the K1 phase) depends on no summed scalar: bit-identical between the two paths;
+    w and r agree to the last bits of alpha."""
+    outs = []
+    for mode in ("0", "1"):
+        monkeypatch.setenv("PB200_LOOP", mode)
+        with pb.Solver(pb.default_params(130, 260, max_iter=1)) as s:
+            res = s.solve()
+            assert res.iterations == 1
+            ptr, pitch, nx, ny = s.field_ptr(2)          # p of the last iteration
+            outs.append((fetch_field(ptr, pitch, nx, ny), s.solution()))
+    assert np.array_equal(outs[0][0], outs[1][0])
+    np.testing.assert_allclose(outs[0][1], outs[1][1], rtol=1e-14, atol=0)
+
+
+def test_graph_and_plain_launches_agree_bitwise(monkeypatch):
+    monkeypatch.setenv("PB200_LOOP", "0")          # the two-kernel path (small blocks default to the resident loop)
     outs = []
     for use_graph, check in ((1, 0), (0, 0), (1, 2), (0, 7)):
         with pb.Solver(pb.default_params(120, 90, use_graph=use_graph, check_every=check)) as s:
