@@ -1425,6 +1425,120 @@ __global__ void __launch_bounds__(CL_THREADS, NC <= 2 ? 4 : 3) cell_loop_kernel(
     }
 }
 
+// The same loop for blocks too large to keep in registers but small enough to live in the 126 MB L2: every block walks
+// over its tiles of CL_BX x CL_BY cells (tile t of block b: b, b + blocks, ...) twice per iteration, state in global
+// memory, Ap recomputed in the second pass from the stored p' (the expressions of the first). Same arithmetic, same
+// fixed summation order (tile order inside a thread, then the block and grid sums above).
+__device__ __forceinline__ double cell_Ap(const CellLoopArgs &A, const double *p, const size_t o, const size_t P, const double pc) {
+    const Consts &c = A.c;
+    const double pl = __ldcg(&p[o - 1]), pr = __ldcg(&p[o + 1]), pd = __ldcg(&p[o - P]), pu = __ldcg(&p[o + P]);
+    const double fx_hi = __ddiv_rn(__ldg(&A.a[o + P]) * (pu - pc), c.h1), fx_lo = __ddiv_rn(__ldg(&A.a[o]) * (pc - pd), c.h1); // S4:527
+    const double fy_hi = __ddiv_rn(__ldg(&A.b[o + 1]) * (pr - pc), c.h2), fy_lo = __ddiv_rn(__ldg(&A.b[o]) * (pc - pl), c.h2); // S4:531
+    return c.mih1 * (fx_hi - fx_lo) + c.mih2 * (fy_hi - fy_lo);                                                                  // S4:526-535
+}
+
+__global__ void __launch_bounds__(CL_THREADS, 4) cell_loop_stream_kernel(const CellLoopArgs A) {
+    __shared__ double s_w[2][CL_THREADS / 32];
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    const Geom g = A.g;
+    const Consts &c = A.c;
+    const unsigned nblocks = gridDim.x, bid = blockIdx.x;
+    const int tiles_x = (g.ny + CL_BX - 1) / CL_BX, tiles_y = (g.nx + CL_BY - 1) / CL_BY, ntiles = tiles_x * tiles_y;
+    const int tx = (int)(threadIdx.x % CL_BX), ty = (int)(threadIdx.x / CL_BX);
+    const size_t P = (size_t)g.pitch;
+    double zr_old = __ldcg(&A.ctl->zr_old); // init_kernel (S4:820-843)
+    double alpha = 0.0, beta = 0.0, diff = 0.0, denom = 0.0;
+    long long k = 0;
+    int status = STOP_MAX_ITER, conv_iter = 0;
+    for (;;) {
+        ++k; // S4:847-848
+        const double *p_old = A.p[(k - 1) & 1];
+        double *p_new = A.p[k & 1];
+        const bool first = k == 1;
+        // ---- K1: p' = D^-1 r + beta p (S4:559, 675; first: p = z, S4:830), all cells of the block's tiles
+        for (int t = (int)bid; t < ntiles; t += (int)nblocks) {
+            const int li = 1 + (t / tiles_x) * CL_BY + ty, lj = 1 + (t % tiles_x) * CL_BX + tx;
+            if (li <= g.nx && lj <= g.ny) {
+                const size_t o = (size_t)li * P + lj;
+                const double z = precond_div(__ldcg(&A.r[o]), __ldg(&A.D[o]));
+                __stcg(&p_new[o], first ? z : z + beta * __ldcg(&p_old[o]));
+            }
+        }
+        grid.sync(); // the stencil needs the neighbours' p'
+        double s1[1] = {0.0};
+        for (int t = (int)bid; t < ntiles; t += (int)nblocks) {
+            const int li = 1 + (t / tiles_x) * CL_BY + ty, lj = 1 + (t % tiles_x) * CL_BX + tx;
+            if (li <= g.nx && lj <= g.ny) {
+                const size_t o = (size_t)li * P + lj;
+                const double pc = __ldcg(&p_new[o]);
+                s1[0] += cell_Ap(A, p_new, o, P, pc) * pc; // S4:594
+            }
+        }
+        grid_sum_all<1>(s1, A.partials, nblocks, bid, s_w, grid);
+        denom = s1[0] * c.h1 * c.h2; // S3:191
+        const bool brk = (c.norm_mode == 1) ? (denom < 1e-15) : (fabs(denom) < 1e-15); // S0:128 | S4:876
+        if (brk) {
+            status = STOP_DENOM;
+            break;
+        }
+        // ---- K2: the updates and the two sums
+        alpha = zr_old / denom; // S4:877
+        double s2[2] = {0.0, 0.0};
+        for (int t = (int)bid; t < ntiles; t += (int)nblocks) {
+            const int li = 1 + (t / tiles_x) * CL_BY + ty, lj = 1 + (t % tiles_x) * CL_BX + tx;
+            if (li <= g.nx && lj <= g.ny) {
+                const size_t o = (size_t)li * P + lj;
+                const double pc = __ldcg(&p_new[o]);
+                const double Ap = cell_Ap(A, p_new, o, P, pc);
+                const double w0 = __ldcg(&A.w[o]);
+                const double wn = w0 + alpha * pc;               // S4:647
+                const double rn = __ldcg(&A.r[o]) - alpha * Ap;  // S4:648
+                const double d = wn - w0;                        // S4:653
+                __stcg(&A.w[o], wn);
+                __stcg(&A.r[o], rn);
+                s2[0] += d * d;
+                s2[1] += precond_div(rn, __ldg(&A.D[o])) * rn; // S4:559, 594
+            }
+        }
+        grid_sum_all<2>(s2, A.partials + nblocks, nblocks, bid, s_w, grid);
+        // ---- the scalar tail (finalize_iteration), in every thread
+        const double zr_new = s2[1] * c.h1 * c.h2;
+        diff = (c.norm_mode == 0) ? sqrt(s2[0] * c.h1 * c.h2) : sqrt(s2[0]); // S3:449 | S0:154
+        const bool conv = diff < c.delta;                                     // S4:899
+        const bool tr = A.trace && k <= c.trace_len && bid == 0 && threadIdx.x == 0;
+        if (tr) {
+            A.trace[3 * (k - 1) + 0] = alpha;
+            A.trace[3 * (k - 1) + 1] = 0.0;
+            A.trace[3 * (k - 1) + 2] = diff;
+        }
+        if (conv && conv_iter == 0) conv_iter = (int)k;
+        if (conv && !c.fixed) {
+            status = STOP_CONVERGED;
+            break;
+        }
+        beta = zr_new / zr_old; // S4:931
+        zr_old = zr_new;        // S4:932
+        if (tr) A.trace[3 * (k - 1) + 1] = beta;
+        if (k >= c.max_iter) { // S4:847: loop bound
+            status = STOP_MAX_ITER;
+            break;
+        }
+    }
+    if (bid == 0 && threadIdx.x == 0) {
+        Ctl *ctl = A.ctl;
+        ctl->zr_old = zr_old;
+        ctl->denom = denom;
+        ctl->alpha = alpha;
+        ctl->beta = beta;
+        ctl->diff = diff;
+        ctl->iter = k;
+        ctl->status = status;
+        ctl->conv_iter = conv_iter;
+        __threadfence();
+        ctl->done = 1;
+    }
+}
+
 // Multi-GPU: after the all-reduce of red[1..2] (or red[2] at init) every rank runs the same scalar tail.
 __global__ void finalize_kernel(Ctl *ctl, Consts c, double *trace, int init) {
     if (stopped(ctl)) return;

@@ -276,6 +276,20 @@ void Solver::plan_launch() {
                 break;
             }
         }
+        // too large for registers, small enough for the L2: the streaming form of the loop (loop_cells = 0)
+        const double pts_local = static_cast<double>(f.g.nx) * f.g.ny;
+        double stream_max = LOOP_STREAM_MAX_POINTS;
+        if (const char *e = std::getenv("PB200_LOOP_STREAM_MAX")) stream_max = atof(e);
+        if (!use_loop && pts_local <= stream_max) {
+            int occS = 0;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occS, cell_loop_stream_kernel, CL_THREADS, 0);
+            const long long tiles = static_cast<long long>((f.g.ny + CL_BX - 1) / CL_BX) * ((f.g.nx + CL_BY - 1) / CL_BY);
+            if (occS > 0) {
+                use_loop = true;
+                loop_cells = 0;
+                loop_grid = dim3(static_cast<unsigned>(std::min<long long>(tiles, static_cast<long long>(occS) * sms)), 1, 1);
+            }
+        }
     }
     norms_grid = dim3((f.g.ny + 255) / 256, std::min(f.g.nx, 512), 1);
     init_grid = dim3((f.g.ny + INIT_THREADS - 1) / INIT_THREADS, std::min(f.g.nx, 1024), 1);
@@ -483,7 +497,8 @@ pb200_status Solver::solve(pb200_result *res) {
         la.g = f.g;
         la.c = c;
         void *args[] = {&la};
-        const void *fn = loop_cells == 1   ? reinterpret_cast<const void *>(cell_loop_kernel<1>)
+        const void *fn = loop_cells == 0   ? reinterpret_cast<const void *>(cell_loop_stream_kernel)
+                         : loop_cells == 1 ? reinterpret_cast<const void *>(cell_loop_kernel<1>)
                          : loop_cells == 2 ? reinterpret_cast<const void *>(cell_loop_kernel<2>)
                                            : reinterpret_cast<const void *>(cell_loop_kernel<4>);
         CK(cudaLaunchCooperativeKernel(fn, loop_grid, dim3(CL_THREADS, 1, 1), args, 0, stream));

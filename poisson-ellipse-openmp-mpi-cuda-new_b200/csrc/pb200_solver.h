@@ -32,6 +32,9 @@ struct MarchPlan {
     Bands bands; // how the rows are cut
 };
 MarchPlan march_plan(int resident_blocks, int wn, int nx);
+// single-GPU blocks of at most this many cells that do not fit cell_loop_kernel run cell_loop_stream_kernel (measured
+// cross-over with the marching kernels)
+constexpr double LOOP_STREAM_MAX_POINTS = 1.3e6;
 
 // The device arrays of one block. Hot (touched every iteration): w, r, p[0], p[1] (ping-pong) and one class
 // byte per cell. Cold (written once by setup, read only on cells cut by the ellipse): a, b, D.
@@ -67,7 +70,7 @@ struct Solver {
     MarchPlan k1_plan{}, k2_plan{};
     bool use_loop = false; // small block: the whole loop is one cooperative launch (cell_loop_kernel)
     dim3 loop_grid;
-    int loop_cells = 1; // cells per thread of cell_loop_kernel
+    int loop_cells = 1; // cells per thread of cell_loop_kernel; 0: cell_loop_stream_kernel
     long long launches = 0;
     long long last_iter = 0;
     double t_setup = 0.0;

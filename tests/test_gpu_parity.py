@@ -280,10 +280,10 @@ def test_solve_800x1200(oracle, golden):
 
 @pytest.mark.parametrize("m,n,kw", [(10, 10, {}), (40, 40, {}), (120, 90, {}), (400, 600, {}), (37, 53, {"norm_mode": 1}),
                                     (100, 140, {"fixed_iters": 75}), (64, 64, {"max_iter": 9}), (65, 300, {"eps": 1e-3}),
-                                    (500, 640, {}), (2, 2, {}), (3, 130, {})])
+                                    (500, 640, {}), (2, 2, {}), (3, 130, {}), (800, 1200, {}), (700, 900, {"fixed_iters": 40})])
 def test_resident_loop_and_two_kernel_paths_agree(monkeypatch, m, n, kw):
     """Small single-GPU blocks run the whole loop as one cooperative launch with a resident thread per cell
-    (cell_loop_kernel: 1, 2 or 4 cells per thread); PB200_LOOP=0 forces the two marching kernels. Element-wise arithmetic
+    (cell_loop_kernel: 1, 2 or 4 cells per thread; above 454 K cells cell_loop_stream_kernel); PB200_LOOP=0 forces the two marching kernels. Element-wise arithmetic
     is the same term by term, the grouping of the partial sums is not: iteration counts are equal, the per-iteration
     scalars agree to 1e-10, the solution to 1e-12 (the same bar as between GPU counts)."""
     if "norm_mode" in kw:
