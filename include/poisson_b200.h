@@ -90,8 +90,10 @@ typedef struct pb200_result {
     double algo_gbps;            /* pt_it_per_s * 104 B */
     int64_t kernel_launches;     /* launches of this library's kernels during the call */
     double t_device_s;           /* device time of the whole pb200_solve call (re-setup, init, loop, norms), CUDA events */
-    double safe_mode;            /* 1.0 if the run used IEEE divides everywhere (data or coefficients left the range in which
-                                    the fast exact divisions are proven, |x| in 2^-400..2^400), else 0.0 */
+    double safe_mode;            /* 1.0 if the run used IEEE divides in every row: the coefficients (1/eps) lie outside
+                                    2^-50..2^300 or a grid step exceeds 2^10, the window in which the fast exact divisions
+                                    are proven. 0.0 otherwise; single rows whose data leave 2^-840..2^601 still fall back
+                                    to IEEE divides on their own. */
     double reserved[4];
 } pb200_result;
 

@@ -17,6 +17,20 @@ struct pb200_solver {
 
 namespace {
 
+// The entry points make the handle's device current for their own work and hand the caller's device back on return.
+struct DeviceGuard {
+    int saved = -1;
+    DeviceGuard() {
+        if (cudaGetDevice(&saved) != cudaSuccess) {
+            cudaGetLastError();
+            saved = -1;
+        }
+    }
+    ~DeviceGuard() {
+        if (saved >= 0) cudaSetDevice(saved);
+    }
+};
+
 // A scratch block for the operator entry points: fields + control words, host arrays in/out.
 struct OpBlock {
     Fields f;
@@ -272,6 +286,7 @@ pb200_status pb200_decompose_2d(int32_t M, int32_t N, int32_t Px, int32_t Py, in
 
 pb200_status pb200_create(const pb200_params *p, pb200_solver **out) {
     if (!p || !out) { set_error("null argument"); return PB200_ERR_INVALID; }
+    DeviceGuard guard;
     *out = nullptr;
     pb200_solver *s = new (std::nothrow) pb200_solver();
     if (!s) { set_error("out of host memory"); return PB200_ERR_INVALID; }
@@ -291,31 +306,37 @@ pb200_status pb200_comm_unique_id(uint8_t id_out[128]) {
 
 pb200_status pb200_attach_comm(pb200_solver *s, const uint8_t unique_id[128]) {
     if (!s || !unique_id) { set_error("null argument"); return PB200_ERR_INVALID; }
+    DeviceGuard guard;
     return s->impl.attach_comm(unique_id);
 }
 
 pb200_status pb200_peer_export(pb200_solver *s, uint8_t blob_out[256]) {
     if (!s || !blob_out) { set_error("null argument"); return PB200_ERR_INVALID; }
+    DeviceGuard guard;
     return s->impl.peer_export(blob_out);
 }
 
 pb200_status pb200_peer_attach(pb200_solver *s, const uint8_t *blobs, int32_t nranks) {
     if (!s || !blobs) { set_error("null argument"); return PB200_ERR_INVALID; }
+    DeviceGuard guard;
     return s->impl.peer_attach(blobs, nranks);
 }
 
 pb200_status pb200_solve(pb200_solver *s, pb200_result *res) {
     if (!s) { set_error("null solver"); return PB200_ERR_INVALID; }
+    DeviceGuard guard;
     return s->impl.solve(res);
 }
 
 pb200_status pb200_get_solution(pb200_solver *s, double *host, int64_t ld) {
     if (!s) { set_error("null solver"); return PB200_ERR_INVALID; }
+    DeviceGuard guard;
     return s->impl.get_solution(host, ld);
 }
 
 pb200_status pb200_get_trace(pb200_solver *s, double *host_3n, int32_t n, int32_t *rows) {
     if (!s || (!host_3n && n > 0)) { set_error("null argument"); return PB200_ERR_INVALID; }
+    DeviceGuard guard;
     int r = 0;
     pb200_status st = s->impl.get_trace(host_3n, n, &r);
     if (rows) *rows = r;
@@ -336,10 +357,14 @@ pb200_status pb200_get_field(pb200_solver *s, int32_t which, double **dev_ptr, i
 
 pb200_status pb200_profile_iteration(pb200_solver *s, int32_t iters, double ms_out[2]) {
     if (!s || !ms_out) { set_error("null argument"); return PB200_ERR_INVALID; }
+    DeviceGuard guard;
     return s->impl.profile_iteration(iters, ms_out);
 }
 
-void pb200_destroy(pb200_solver *s) { delete s; }
+void pb200_destroy(pb200_solver *s) {
+    DeviceGuard guard;
+    delete s;
+}
 
 // pb200_run keeps the handle of its last call (per host thread): an identical call then skips the device allocation
 // and the coefficient kernel, which at 8192^2 cost about as much as 15 iterations.
@@ -351,20 +376,36 @@ struct RunCache {
 thread_local RunCache g_run_cache;
 } // namespace
 
-void pb200_release_cache(void) { g_run_cache.solver.reset(); }
+void pb200_release_cache(void) {
+    DeviceGuard guard;
+    g_run_cache.solver.reset();
+}
 
 pb200_status pb200_run(const pb200_params *p, pb200_result *res, double *w_host, int64_t ld) {
     if (!p) { set_error("null argument"); return PB200_ERR_INVALID; }
     if (p->nranks != 1) { set_error("pb200_run is single-rank; use create/attach_comm/solve"); return PB200_ERR_INVALID; }
+    DeviceGuard guard;
     RunCache &rc = g_run_cache;
-    const bool reuse = rc.solver && std::memcmp(&rc.params, p, sizeof(*p)) == 0 && !std::getenv("PB200_NO_CACHE");
+    // the cache key names the device explicitly: "the current device" (device < 0) is resolved first, so a caller that
+    // switched devices between two otherwise identical calls gets a workspace on the new device
+    pb200_params key = *p;
+    if (key.device < 0) {
+        int cur = 0;
+        if (cudaGetDevice(&cur) != cudaSuccess) {
+            cudaGetLastError();
+            set_error("no CUDA device: libpoisson_b200 has no CPU path");
+            return PB200_ERR_CUDA;
+        }
+        key.device = cur;
+    }
+    const bool reuse = rc.solver && std::memcmp(&rc.params, &key, sizeof(key)) == 0 && !std::getenv("PB200_NO_CACHE");
     double t_setup = 0.0;
     if (!reuse) {
         rc.solver.reset(); // free the previous workspace before allocating the next
         pb200_solver *s = nullptr;
-        TRY(pb200_create(p, &s));
+        TRY(pb200_create(&key, &s));
         rc.solver.reset(s);
-        rc.params = *p;
+        rc.params = key;
         t_setup = s->impl.t_setup;
     }
     Solver &S = rc.solver->impl;
@@ -490,10 +531,12 @@ pb200_status pb200_selftest_div(double h, int64_t n, uint64_t seed, int64_t *mis
     }
     unsigned long long *d = nullptr;
     CK(cudaMalloc(&d, sizeof(unsigned long long)));
-    CK(cudaMemset(d, 0, sizeof(unsigned long long)));
-    selftest_div_kernel<<<296, 256>>>(h, 1.0 / h, n, seed, d);
     unsigned long long bad = 0;
-    cudaError_t e = cudaMemcpy(&bad, d, sizeof(bad), cudaMemcpyDeviceToHost);
+    cudaError_t e = cudaMemset(d, 0, sizeof(unsigned long long));
+    if (e == cudaSuccess) {
+        selftest_div_kernel<<<296, 256>>>(h, 1.0 / h, n, seed, d);
+        e = cudaMemcpy(&bad, d, sizeof(bad), cudaMemcpyDeviceToHost);
+    }
     cudaFree(d);
     CK(e);
     *mismatches = static_cast<int64_t>(bad);

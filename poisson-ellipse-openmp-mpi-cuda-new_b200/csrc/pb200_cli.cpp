@@ -129,25 +129,39 @@ int main(int argc, char **argv) {
         return 1;
     }
     std::vector<uint8_t> blobs(static_cast<size_t>(gpus) * 256);
-    std::atomic<int> exported{0}, failed{0};
+    std::atomic<int> created{0}, exported{0}, failed{0};
     auto rank_main = [&](int rank) {
         pb200_params p = prm;
         p.nranks = gpus;
         p.rank = rank;
         p.device = first_device + rank;
         auto fail = [&](pb200_status st) {
+            failed = 1;
             status[rank] = st;
             errors[rank] = pb200_last_error();
         };
+        // Every rank reaches each meeting point whether its own step worked or not, and all of them take the same decision
+        // there: a rank that failed never leaves the others waiting inside a collective.
+        auto meet = [&](std::atomic<int> &counter) {
+            ++counter;
+            while (counter.load() < gpus) std::this_thread::yield();
+            return failed.load() == 0;
+        };
         pb200_status st = pb200_create(&p, &solvers[rank]);
-        if (st != PB200_OK) return fail(st);
-        if (gpus > 1 && (st = pb200_attach_comm(solvers[rank], uid)) != PB200_OK) { failed = 1; return fail(st); }
+        if (st != PB200_OK) fail(st);
+        if (gpus > 1 && !meet(created)) {
+            if (status[rank] == PB200_OK) { status[rank] = PB200_ERR_STATE; errors[rank] = "another rank failed during set-up"; }
+            return;
+        }
+        if (st != PB200_OK) return;
+        if (gpus > 1 && (st = pb200_attach_comm(solvers[rank], uid)) != PB200_OK) return fail(st);
         if (gpus > 1 && peer_mode) { // every rank publishes where its mailbox / residual live, then maps the others'
             st = pb200_peer_export(solvers[rank], blobs.data() + 256 * rank);
-            if (st != PB200_OK) failed = 1;
-            ++exported;
-            while (exported.load() < gpus && !failed.load()) std::this_thread::yield();
-            if (failed.load()) return fail(st != PB200_OK ? st : PB200_ERR_COMM);
+            if (st != PB200_OK) fail(st);
+            if (!meet(exported)) {
+                if (status[rank] == PB200_OK) { status[rank] = PB200_ERR_COMM; errors[rank] = "another rank failed during set-up"; }
+                return;
+            }
             if ((st = pb200_peer_attach(solvers[rank], blobs.data(), gpus)) != PB200_OK) return fail(st);
         }
         if ((st = pb200_solve(solvers[rank], &results[rank])) != PB200_OK) return fail(st);

@@ -127,6 +127,7 @@ pb200_status Solver::attach_comm(const uint8_t id_bytes[128]) {
 }
 
 bool Solver::comm_ready() const { return comm && comm->nc; }
+bool Solver::comm_failed() const { return comm && comm->async_err != ncclSuccess; }
 
 void Solver::destroy_comm() {
     if (!comm) return;
@@ -283,6 +284,11 @@ void Solver::peer_release() {
 }
 
 pb200_status Solver::reduce_norms_host(double *) {
+    if (comm->async_err != ncclSuccess) { // the loop stopped launching when it saw this
+        set_error("NCCL error during the loop: %s", nccl().GetErrorString(comm->async_err));
+        comm->async_err = ncclSuccess;
+        return PB200_ERR_COMM;
+    }
     // in-stream: sums of w^2, r^2 and the max |w| (bit pattern of a non-negative double orders like uint64)
     NK(nccl().AllReduce(norms, norms, 2, ncclDouble, ncclSum, comm->nc, stream));
     NK(nccl().AllReduce(norms + 2, norms + 2, 1, ncclUint64, ncclMax, comm->nc, stream));

@@ -470,10 +470,14 @@ pb200_status Solver::solve(pb200_result *res) {
     CK(cudaGetLastError());
 
     // ---- loop (S4:845-943)
-    const double pts_local = static_cast<double>(f.g.nx) * f.g.ny;
+    // The poll interval must be the same on every rank: in NCCL mode a rank that leaves the loop after a different
+    // number of launched iterations would issue collectives the others do not match. So it is derived from the global
+    // grid and the rank count, never from this rank's own block (blocks differ by a row or a column); an explicit
+    // check_every has to be the same number on all ranks.
+    const double pts_rank = static_cast<double>(prm.M - 1) * (prm.N - 1) / prm.nranks;
     int check = prm.check_every;
     if (check <= 0) { // poll roughly every 250 us of device work
-        const double t_it = std::max(6e-6, pts_local * 112.0 / 6.0e12);
+        const double t_it = std::max(6e-6, pts_rank * 112.0 / 6.0e12);
         check = static_cast<int>(std::min(64.0, std::max(2.0, 250e-6 / t_it)));
     }
     check += check & 1; // even: graph replays cover two iterations
@@ -515,14 +519,20 @@ pb200_status Solver::solve(pb200_result *res) {
         CK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
         launch_iteration(2, false);
         launch_iteration(3, false);
-        CK(cudaStreamEndCapture(stream, &graph));
-        CK(cudaGraphInstantiate(&graph_exec, graph, 0));
-        cudaGraphDestroy(graph);
+        // whatever happened in between, the capture is ended here, so an error never leaves the stream capturing
+        const cudaError_t e_end = cudaStreamEndCapture(stream, &graph);
+        cudaError_t e_inst = cudaSuccess;
+        if (e_end == cudaSuccess) e_inst = cudaGraphInstantiate(&graph_exec, graph, 0);
+        if (graph) cudaGraphDestroy(graph);
+        if (e_end != cudaSuccess || e_inst != cudaSuccess) graph_exec = nullptr;
+        CK(e_end);
+        CK(e_inst);
     }
     int slot = 0, pending = -1;
     bool done = false;
     long long since_poll = 1;
     while (!done && k <= c.max_iter) {
+        if (comm_failed()) break; // NCCL mode: a collective could not be enqueued; reduce_norms_host reports it
         if (use_graph && graph_exec) {
             CK(cudaGraphLaunch(graph_exec, stream)); // iterations k, k+1 (the second is a no-op past the end)
             launches += 2 * kernels_per_iteration();

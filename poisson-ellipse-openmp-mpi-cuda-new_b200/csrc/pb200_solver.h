@@ -102,6 +102,7 @@ struct Solver {
     // multi-GPU (pb200_comm.cu)
     pb200_status attach_comm(const uint8_t id[128]);
     bool comm_ready() const;
+    bool comm_failed() const; // an NCCL call of the loop returned an error
     void destroy_comm();
     void allreduce(int first, int count); // in place on ctl->red[first .. first+count)
     void exchange_r_halo();               // boundary rows/columns of r -> neighbours' ring

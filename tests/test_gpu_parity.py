@@ -375,14 +375,24 @@ def test_far_past_convergence(oracle):
 
 
 @pytest.mark.parametrize("m,n,want", [(1600, 2400, 1858), (2400, 3200, 2449)])
-def test_long_solves_reference_iteration_counts(m, n, want):
+def test_long_solves_reference_iteration_counts_and_norms(golden, m, n, want):
     """The reference's published counts on its two largest grids, twice: any race in the kernels'
-    shared-memory pipeline shows up here as a run-to-run difference."""
+    shared-memory pipeline shows up here as a run-to-run difference. The norms are checked against the reference's own
+    (tests/golden: ref3_solve_traced through the unmodified stage3 operators). At these sizes the reference's results
+    move by 1.4e-9 (||w||_E) / 4e-11 (||dw||) with its own summation order: the bar is
+    max(1e-10, that spread). These solves run for thousands of iterations on an exterior hundreds of cells deep, so the
+    rows that fall back to IEEE divides (values below 2^-840) are part of what is compared."""
     a, _ = pb.run(pb.default_params(m, n))
     b, _ = pb.run(pb.default_params(m, n))
-    assert a.iterations == b.iterations == want
+    assert a.iterations == b.iterations == want == golden["iters_stage3"][f"{m}x{n}"]
     assert (a.w_norm_E, a.diff_norm, a.zr) == (b.w_norm_E, b.diff_norm, b.zr)
     assert a.safe_mode == 0.0
+    g = golden["solves_stage3"][f"{m}x{n}"]
+    assert rel(a.w_norm_E, g["w_norm_E"]) < 5e-9
+    assert rel(a.w_max, g["w_max"]) < 5e-9
+    assert rel(a.diff_norm, g["diff_norm"]) < 1e-9
+    assert rel(a.zr, g["zr"]) < 1e-8
+    assert rel(a.alpha, g["alpha"]) < 1e-8
 
 
 def test_other_problem_parameters(oracle):
@@ -411,16 +421,55 @@ def test_analytic_solution_error():
 # size-independent properties.
 
 def test_full_size_first_iterations(oracle):
+    """8192 x 8192 (BASELINE configs[3]): the alpha / beta / ||dw|| trace of the first 48 iterations against the oracle
+    (which needs ~0.1 s per iteration at this size), the norms after them, and run-to-run determinism."""
     m = n = 8192
-    k = 3
+    k = 48
     with pb.Solver(pb.default_params(m, n, fixed_iters=k, trace_len=k)) as s:
         res = s.solve()
         trace = s.trace(k)
         res2 = s.solve()            # determinism at full size
     ores, _, otrace = oracle.solve(m, n, fixed_iters=k, trace_len=k)
     assert res.iterations == k
+    np.testing.assert_allclose(trace[:3], otrace[:3], rtol=1e-11, atol=0)
+    np.testing.assert_allclose(trace, otrace, rtol=RTOL_NORM, atol=0)
+    assert rel(res.w_norm_E, ores.w_norm_E) < RTOL_NORM
+    assert rel(res.r_norm_E, ores.r_norm_E) < RTOL_NORM
+    assert rel(res.diff_norm, ores.diff_norm) < RTOL_NORM
+    assert rel(res.zr, ores.zr) < RTOL_NORM
+    assert res.w_max == pytest.approx(ores.w_max, rel=1e-12)
+    assert (res2.zr, res2.diff_norm, res2.w_norm_E) == (res.zr, res.diff_norm, res.w_norm_E)
+
+
+def _mem_available_gb():
+    try:
+        for ln in open("/proc/meminfo"):
+            if ln.startswith("MemAvailable:"):
+                return int(ln.split()[1]) / 2 ** 20
+    except OSError:
+        pass
+    return 0.0
+
+
+def test_largest_grid_first_iterations(oracle):
+    """BASELINE configs[4]: 32768 x 32768 (1.07e9 unknowns, 60 GB on the GPU) against the oracle for the first two
+    iterations -- offsets beyond 2^31, the power-of-two step in x. The oracle holds eight full arrays (69 GB at this size):
+    when the host has less memory than that the test runs the half grid 16384 x 32768 (34 GB) instead, and says so."""
+    avail = _mem_available_gb()
+    if avail >= 84:
+        m, n = 32768, 32768
+    elif avail >= 42:
+        m, n = 16384, 32768
+    else:
+        pytest.skip(f"host has {avail:.0f} GB available: the oracle needs 34 GB even for 16384 x 32768")
+    print(f"largest-grid check on {m} x {n} (host memory available: {avail:.0f} GB)")
+    k = 2
+    with pb.Solver(pb.default_params(m, n, fixed_iters=k, trace_len=k)) as s:
+        res = s.solve()
+        trace = s.trace(k)
+    ores, _, otrace = oracle.solve(m, n, fixed_iters=k, trace_len=k)
+    assert res.iterations == k and res.safe_mode == 0.0
     np.testing.assert_allclose(trace, otrace, rtol=1e-11, atol=0)
     assert rel(res.w_norm_E, ores.w_norm_E) < RTOL_NORM
     assert rel(res.r_norm_E, ores.r_norm_E) < RTOL_NORM
     assert res.w_max == pytest.approx(ores.w_max, rel=1e-12)
-    assert (res2.zr, res2.diff_norm, res2.w_norm_E) == (res.zr, res.diff_norm, res.w_norm_E)
