@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define PB200_API_VERSION 1
+#define PB200_API_VERSION 2 /* 2: rhs_mode, ell_ax (taken from v1's reserved words: a zeroed v1 struct means the same), analytic error in the result */
 
 typedef enum pb200_status {
     PB200_OK = 0,
@@ -35,6 +35,16 @@ typedef enum pb200_status {
 enum {
     PB200_NORM_WEIGHTED = 0, /* stages 1-4: sqrt(sum dw^2 * h1*h2) (S4:659,897; S3:449); guard |denom| < 1e-15 (S4:876) */
     PB200_NORM_STAGE0 = 1    /* stage0: sqrt(sum dw^2) (S0:149-154); guard denom < 1e-15 (S0:128) */
+};
+
+/* Right-hand side. */
+enum {
+    PB200_RHS_INDICATOR = 0, /* the reference: B_ij = f if node (x_i,y_j) lies in D, else 0 (S4:182-191) */
+    PB200_RHS_AREA = 1       /* no reference counterpart (BASELINE north_star's "area fractions"): B_ij = f * share of the cell
+                                [x_i-h1/2, x_i+h1/2] x [y_j-h2/2, y_j+h2/2] inside D, computed as the area of the polygon
+                                spanned by the end points of the in-D parts of the cell's four edges (the edge intersections of
+                                S4:46-76): the cell clipped by the chords of the ellipse. Changes every number of the solve,
+                                so it is never the default. */
 };
 
 /* Why the loop ended. */
@@ -56,7 +66,7 @@ typedef struct pb200_params {
     int64_t max_iter;      /* <= 0: (M-1)*(N-1) (S4:1007) */
     double A1, B1, A2, B2; /* rectangle (S4:11-12: -1,1,-0.6,0.6) */
     double f_val;          /* right-hand side inside D (S4:13: 1.0); RHS is the point indicator (S4:182-191) */
-    double ell_k;          /* domain D = { x^2 + (ell_k*y)^2 < 1 } (S4:32-34: ell_k = 2) */
+    double ell_k;          /* domain D = { (x/ell_ax)^2 + (ell_k*y)^2 < 1 } (S4:32-34: ell_k = 2, ell_ax = 1) */
     double eps;            /* fictitious-domain penalty; <= 0: max(h1,h2)^2 (S4:693) */
     int32_t norm_mode;     /* PB200_NORM_* */
     int32_t fixed_iters;   /* > 0: run exactly this many iterations; the delta test is evaluated and recorded
@@ -69,7 +79,10 @@ typedef struct pb200_params {
     int32_t rank;          /* 0..nranks-1; rank -> (px,py) = (rank % Px, rank / Px) (S4:100-101) */
     int32_t Px, Py;        /* <= 0: pb200_choose_process_grid(nranks) */
     int32_t use_graph;     /* 1: replay the iteration as a CUDA graph (default); 0: plain launches */
-    int32_t reserved[7];
+    int32_t rhs_mode;      /* PB200_RHS_*; 0 = the reference's indicator */
+    int32_t reserved0;
+    double ell_ax;         /* x semi-axis of the ellipse; <= 0: 1.0 (the reference, S4:32-34) */
+    int32_t reserved[4];
 } pb200_params;
 
 /* What the reference prints (S4:901-903, 969-980, 1027-1035) plus what it never exposed. */
@@ -94,7 +107,11 @@ typedef struct pb200_result {
                                     2^-50..2^300 or a grid step exceeds 2^10, the window in which the fast exact divisions
                                     are proven. 0.0 otherwise; single rows whose data leave 2^-840..2^601 still fall back
                                     to IEEE divides on their own. */
-    double reserved[4];
+    double err_max_in_D;         /* max |w - u| over the nodes inside D, u = f (1 - (x/ax)^2 - (k y)^2) / (2/ax^2 + 2 k^2) the
+                                    analytic solution on D (R4 p.1-2: (1 - x^2 - 4 y^2)/10); all ranks. The reference states u
+                                    but never compares: it frees w unseen (S4:946-954). */
+    double err_l2_in_D;          /* sqrt(sum_{nodes in D} (w - u)^2 h1 h2) */
+    double reserved[2];
 } pb200_result;
 
 typedef struct pb200_solver pb200_solver;

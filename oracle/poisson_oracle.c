@@ -28,23 +28,30 @@ void po_default_problem(po_problem *pb) {
     pb->f_val = 1.0; /* S4:13 */
     pb->ell_k = 2.0; /* S4:33: x*x + 4.0*y*y */
     pb->eps = 0.0;   /* S4:693 */
+    pb->ell_ax = 1.0; /* S4:33: x*x */
+    pb->rhs_mode = 0; /* S4:182-191 */
 }
 
-/* S4:32-34 (S3:19-21): x*x + 4.0*y*y < 1.0; 4.0 = k*k, product evaluated left to right. */
+static double ell_ax(const po_problem *pb) { return pb->ell_ax > 0.0 ? pb->ell_ax : 1.0; }
+
+/* S4:32-34 (S3:19-21): x*x + 4.0*y*y < 1.0; 4.0 = k*k, product evaluated left to right. With the x semi-axis ax of
+ * the generalised ellipse, x*x is scaled by 1/(ax*ax): 1.0 for the reference's ax = 1, an exact product. */
 int po_is_in_D(const po_problem *pb, double x, double y) {
     double c = pb->ell_k * pb->ell_k;
-    return (x * x + c * y * y < 1.0);
+    double inv_ax2 = 1.0 / (ell_ax(pb) * ell_ax(pb));
+    return (x * x * inv_ax2 + c * y * y < 1.0);
 }
 
 /* S4:46-76 (S3:33-55). */
 double po_segment_length(const po_problem *pb, double cc, double s, double e, int vertical) {
     double c = pb->ell_k * pb->ell_k;
+    double ax = ell_ax(pb), inv_ax2 = 1.0 / (ax * ax); /* reference: 1, 1 */
     double lij;
     if (vertical) {
         double x0 = cc;
-        if (fabs(x0) >= 1.0) lij = 0.0;
+        if (fabs(x0) >= ax) lij = 0.0; /* S4:51: abs(x0) >= 1.0 */
         else {
-            double root = sqrt(dmax(0.0, (1.0 - x0 * x0) / c)); /* S4:53-54 */
+            double root = sqrt(dmax(0.0, (1.0 - x0 * x0 * inv_ax2) / c)); /* S4:53-54 */
             double y_min = -root, y_max = root;
             lij = dmax(0.0, dmin(e, y_max) - dmax(s, y_min)); /* S4:55 */
         }
@@ -52,7 +59,7 @@ double po_segment_length(const po_problem *pb, double cc, double s, double e, in
         double y0 = cc;
         if (fabs(pb->ell_k * y0) >= 1.0) lij = 0.0; /* S4:59: abs(2.0*y0) >= 1.0 */
         else {
-            double root = sqrt(dmax(0.0, 1.0 - c * y0 * y0)); /* S4:61-62 */
+            double root = ax * sqrt(dmax(0.0, 1.0 - c * y0 * y0)); /* S4:61-62 */
             double x_min = -root, x_max = root;
             lij = dmax(0.0, dmin(e, x_max) - dmax(s, x_min)); /* S4:63 */
         }
@@ -88,6 +95,75 @@ static void grid_steps(const po_problem *pb, int M, int N, double *h1, double *h
     *eps = pb->eps > 0.0 ? pb->eps : dmax(*h1, *h2) * dmax(*h1, *h2); /* S4:693 */
 }
 
+/* The part [*lo, *hi] of a cell edge that lies in D: the two clamped end points whose difference
+ * po_segment_length returns (S4:46-76, same expressions). Returns 0 when the edge misses D. */
+static int segment_ends(const po_problem *pb, double cc, double s, double e, int vertical, double *lo, double *hi) {
+    double c = pb->ell_k * pb->ell_k;
+    double ax = ell_ax(pb), inv_ax2 = 1.0 / (ax * ax);
+    double root;
+    if (vertical) {
+        if (fabs(cc) >= ax) return 0;                               /* S4:51 */
+        root = sqrt(dmax(0.0, (1.0 - cc * cc * inv_ax2) / c));      /* S4:53-54 */
+    } else {
+        if (fabs(pb->ell_k * cc) >= 1.0) return 0;                  /* S4:59 */
+        root = ax * sqrt(dmax(0.0, 1.0 - c * cc * cc));             /* S4:61-62 */
+    }
+    *lo = dmax(s, -root); /* S4:55, 63 */
+    *hi = dmin(e, root);
+    return *hi > *lo;
+}
+
+/* Running shoelace sum over the vertices of a polygon given in order. */
+typedef struct shoelace {
+    int n;
+    double x0, y0, xp, yp, sum;
+} shoelace;
+static void shoelace_add(shoelace *q, double x, double y) {
+    if (q->n == 0) {
+        q->x0 = x;
+        q->y0 = y;
+    } else
+        q->sum += q->xp * y - x * q->yp;
+    q->xp = x;
+    q->yp = y;
+    q->n++;
+}
+
+/* Area-fraction right-hand side (rhs_mode 1; no reference counterpart): f times the share of the node's cell
+ * [x_i - h1/2, x_{i+1} - h1/2] x [y_j - h2/2, y_{j+1} - h2/2] that lies in D. The share is the area of the polygon whose
+ * vertices are the end points of the in-D parts of the cell's four edges (the edge intersections of S4:46-76; the
+ * cell's right / upper edges are the left / lower edges of nodes (gi+1,gj) / (gi,gj+1)), walked counter-clockwise,
+ * in coordinates relative to the node -- the cell clipped by the chords of the ellipse, second-order accurate.
+ * Snapped to 0 / 1 with the reference's 1e-9 threshold: cells wholly inside get exactly f. */
+static double rhs_area(const po_problem *pb, int gi, int gj, double h1, double h2) {
+    double x_i = pb->A1 + gi * h1, y_j = pb->A2 + gj * h2;           /* S4:159-160 */
+    double x_ip = pb->A1 + (gi + 1) * h1, y_jp = pb->A2 + (gj + 1) * h2;
+    double xl = x_i - 0.5 * h1, xr = x_ip - 0.5 * h1, yb = y_j - 0.5 * h2, yt = y_jp - 0.5 * h2;
+    double lo, hi, frac;
+    shoelace q = {0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    if (segment_ends(pb, yb, xl, xr, 0, &lo, &hi)) { /* bottom edge, left to right */
+        shoelace_add(&q, lo - x_i, yb - y_j);
+        shoelace_add(&q, hi - x_i, yb - y_j);
+    }
+    if (segment_ends(pb, xr, yb, yt, 1, &lo, &hi)) { /* right edge, upwards */
+        shoelace_add(&q, xr - x_i, lo - y_j);
+        shoelace_add(&q, xr - x_i, hi - y_j);
+    }
+    if (segment_ends(pb, yt, xl, xr, 0, &lo, &hi)) { /* top edge, right to left */
+        shoelace_add(&q, hi - x_i, yt - y_j);
+        shoelace_add(&q, lo - x_i, yt - y_j);
+    }
+    if (segment_ends(pb, xl, yb, yt, 1, &lo, &hi)) { /* left edge, downwards */
+        shoelace_add(&q, xl - x_i, hi - y_j);
+        shoelace_add(&q, xl - x_i, lo - y_j);
+    }
+    if (q.n == 0) return 0.0;
+    q.sum += q.xp * q.y0 - q.x0 * q.yp;
+    frac = (0.5 * q.sum) / (h1 * h2);
+    frac = (fabs(frac - 1.0) < 1e-9) ? 1.0 : (frac < 1e-9 ? 0.0 : frac);
+    return pb->f_val * frac;
+}
+
 /* S4:146-192 (S3:126-175). */
 void po_setup_local(const po_problem *pb, int M, int N, int i0, int i1, int j0, int j1, double *a, double *b, double *B) {
     double h1, h2, eps;
@@ -107,7 +183,8 @@ void po_setup_local(const po_problem *pb, int M, int N, int i0, int i1, int j0, 
             b[IDX(li, lj, ny)] = (fabs(lb - h1) < 1e-9) ? 1.0
                                  : (lb < 1e-9 ? 1.0 / eps : (lb / h1) + (1.0 - lb / h1) / eps); /* S4:173-177 */
             if (gi >= i0 && gi <= i1 && gj >= j0 && gj <= j1)
-                B[IDX(li, lj, ny)] = po_is_in_D(pb, x_i, y_j) ? pb->f_val : 0.0; /* S4:182-191 */
+                B[IDX(li, lj, ny)] = pb->rhs_mode == 1 ? rhs_area(pb, gi, gj, h1, h2)
+                                                       : (po_is_in_D(pb, x_i, y_j) ? pb->f_val : 0.0); /* S4:182-191 */
         }
     }
 }
@@ -263,9 +340,10 @@ static void exchange_all(block *bks, int Px, int Py) {
 
 static void finish(const po_problem *pb, block *bks, int P, int M, int N, double h1, double h2, po_result *res,
                    double *w_out) {
-    double ww = 0.0, rr = 0.0, wmax = 0.0, emax = 0.0;
+    double ww = 0.0, rr = 0.0, wmax = 0.0, emax = 0.0, e2 = 0.0;
     double kk = pb->ell_k * pb->ell_k;
-    double scale = pb->f_val / (2.0 + 2.0 * kk); /* u = (1 - x^2 - 4y^2)/10 for k = 2, f = 1 */
+    double inv_ax2 = 1.0 / (ell_ax(pb) * ell_ax(pb));
+    double scale = pb->f_val / (2.0 * inv_ax2 + 2.0 * kk); /* u = (1 - x^2 - 4y^2)/10 for k = 2, ax = 1, f = 1 (R4 p.1-2) */
     if (w_out) memset(w_out, 0, sizeof(double) * (size_t)(M + 1) * (size_t)(N + 1));
     for (int rnk = 0; rnk < P; ++rnk) {
         block *bk = &bks[rnk];
@@ -278,8 +356,9 @@ static void finish(const po_problem *pb, block *bks, int P, int M, int N, double
                 double x = pb->A1 + gi * h1, y = pb->A2 + gj * h2;
                 if (fabs(v) > wmax) wmax = fabs(v);
                 if (po_is_in_D(pb, x, y)) {
-                    double e = fabs(v - scale * (1.0 - x * x - kk * y * y));
+                    double e = fabs(v - scale * (1.0 - x * x * inv_ax2 - kk * y * y));
                     if (e > emax) emax = e;
+                    e2 += e * e;
                 }
                 if (w_out) w_out[(size_t)gi * (size_t)(N + 1) + (size_t)gj] = v;
             }
@@ -288,6 +367,7 @@ static void finish(const po_problem *pb, block *bks, int P, int M, int N, double
     res->r_norm_E = sqrt(rr);
     res->w_max = wmax;
     res->err_max_in_D = emax;
+    res->err_l2_in_D = sqrt(e2 * h1 * h2);
 }
 
 static int solve_impl(const po_problem *pb, int M, int N, double delta, long max_iter, int norm_mode, int fixed_iters,

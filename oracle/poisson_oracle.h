@@ -27,6 +27,9 @@ typedef struct po_problem {
     double f_val;          /* right-hand side inside D, S4:13: 1.0 */
     double ell_k;          /* ellipse x^2 + (k*y)^2 < 1; reference k = 2 (S4:32-34: 4.0*y*y) */
     double eps;            /* <= 0: max(h1,h2)^2 (S4:693) */
+    /* Extensions beyond the reference; the defaults reproduce it bit for bit. */
+    double ell_ax;         /* x semi-axis: ellipse (x/ax)^2 + (k*y)^2 < 1; <= 0: 1.0 (S4:32-34) */
+    int rhs_mode;          /* 0: point indicator (S4:182-191); 1: area fraction of the node's cell (polygon through its edge/ellipse intersections) */
 } po_problem;
 
 void po_default_problem(po_problem *pb);
@@ -44,6 +47,7 @@ typedef struct po_result {
     double r_norm_E;  /* sqrt(sum r^2 h1 h2) */
     double w_max;     /* max |w| */
     double err_max_in_D; /* max |w - (1-x^2-4y^2)/10| over nodes in D (analytic solution, reference report) */
+    double err_l2_in_D;  /* sqrt(sum over nodes in D of (w-u)^2 h1 h2) */
 } po_result;
 
 int po_is_in_D(const po_problem *pb, double x, double y);                          /* S4:32-34 */

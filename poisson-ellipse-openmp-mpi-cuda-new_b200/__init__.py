@@ -17,6 +17,7 @@ LIB_PATH = os.environ.get("PB200_LIB") or os.path.join(HERE, "libpoisson_b200.so
 CLI_PATH = os.path.join(HERE, "poisson_b200")
 
 NORM_WEIGHTED, NORM_STAGE0 = 0, 1
+RHS_INDICATOR, RHS_AREA = 0, 1
 STOP_MAX_ITER, STOP_CONVERGED, STOP_DENOM, STOP_COMM_TIMEOUT = 0, 1, 2, 3
 
 c_double_p = C.POINTER(C.c_double)
@@ -31,7 +32,8 @@ class Params(C.Structure):
                 ("norm_mode", C.c_int32), ("fixed_iters", C.c_int32), ("device", C.c_int32),
                 ("check_every", C.c_int32), ("trace_len", C.c_int32),
                 ("nranks", C.c_int32), ("rank", C.c_int32), ("Px", C.c_int32), ("Py", C.c_int32),
-                ("use_graph", C.c_int32), ("reserved", C.c_int32 * 7)]
+                ("use_graph", C.c_int32), ("rhs_mode", C.c_int32), ("reserved0", C.c_int32), ("ell_ax", C.c_double),
+                ("reserved", C.c_int32 * 4)]
 
 
 class Result(C.Structure):
@@ -42,10 +44,11 @@ class Result(C.Structure):
                 ("w_norm_E", C.c_double), ("r_norm_E", C.c_double), ("w_max", C.c_double),
                 ("t_setup_s", C.c_double), ("t_solve_s", C.c_double), ("t_total_s", C.c_double),
                 ("pt_it_per_s", C.c_double), ("algo_gbps", C.c_double), ("kernel_launches", C.c_int64),
-                ("t_device_s", C.c_double), ("safe_mode", C.c_double), ("reserved", C.c_double * 4)]
+                ("t_device_s", C.c_double), ("safe_mode", C.c_double), ("err_max_in_D", C.c_double),
+                ("err_l2_in_D", C.c_double), ("reserved", C.c_double * 2)]
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+        return {k: getattr(self, k) for k, _ in self._fields_ if not k.startswith("reserved")}
 
 
 class PB200Error(RuntimeError):

@@ -237,6 +237,8 @@ void pb200_default_params(pb200_params *p) {
     p->B2 = 0.6;
     p->f_val = 1.0; // S4:13
     p->ell_k = 2.0; // S4:33
+    p->ell_ax = 1.0; // S4:33: x*x
+    p->rhs_mode = PB200_RHS_INDICATOR; // S4:182-191
     p->eps = 0.0;   // S4:693
     p->norm_mode = PB200_NORM_WEIGHTED;
     p->device = -1;
@@ -384,6 +386,7 @@ void pb200_release_cache(void) {
 pb200_status pb200_run(const pb200_params *p, pb200_result *res, double *w_host, int64_t ld) {
     if (!p) { set_error("null argument"); return PB200_ERR_INVALID; }
     if (p->nranks != 1) { set_error("pb200_run is single-rank; use create/attach_comm/solve"); return PB200_ERR_INVALID; }
+    TRY(validate(*p)); // argument errors come before any device error
     DeviceGuard guard;
     RunCache &rc = g_run_cache;
     // the cache key names the device explicitly: "the current device" (device < 0) is resolved first, so a caller that

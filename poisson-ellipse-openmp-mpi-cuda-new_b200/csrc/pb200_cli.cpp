@@ -27,10 +27,12 @@ static double now_s() {
 
 static void usage() {
     std::cerr <<
-        "usage: poisson_b200 [M N] [--delta D] [--max-iter K] [--eps E] [--ellipse-k K] [--rect A1 B1 A2 B2] [--f F]\n"
+        "usage: poisson_b200 [M N] [--delta D] [--max-iter K] [--eps E] [--ellipse-k K] [--ellipse-ax A] [--rect A1 B1 A2 B2] [--f F]\n"
+        "                    [--rhs indicator|area] [--report-error]\n"
         "                    [--norm weighted|stage0] [--gpus P] [--grid PXxPY] [--device D] [--fixed-iters K]\n"
         "                    [--trace K] [--check-every K] [--no-graph] [--comm peer|nccl] [--dump FILE(.npy|.txt|raw)] [--json FILE|-]\n"
-        "Solves -div(k grad u) = f on the rectangle with the ellipse x^2+(k y)^2<1 as fictitious domain (PCG).\n"
+        "Solves -div(k grad u) = f on the rectangle with the ellipse (x/ax)^2+(k y)^2<1 as fictitious domain (PCG).\n"
+        "--report-error adds a line with max|w-u| and the L2 error against the analytic solution inside the ellipse.\n"
         "With no flags it behaves as the reference: `poisson_b200 M N`.\n";
 }
 
@@ -69,6 +71,7 @@ int main(int argc, char **argv) {
     pb200_default_params(&prm);
     int gpus = 1, first_device = 0;
     bool peer_mode = true; // multi-GPU: halos and sums through peer memory inside the kernels (else NCCL calls per iteration)
+    bool report_error = false;
     std::string dump, json;
     std::vector<const char *> pos;
     for (int i = 1; i < argc; ++i) {
@@ -81,6 +84,9 @@ int main(int argc, char **argv) {
         else if (a == "--eps") { need(1); prm.eps = atof(argv[++i]); }
         else if (a == "--ellipse-k") { need(1); prm.ell_k = atof(argv[++i]); }
         else if (a == "--f") { need(1); prm.f_val = atof(argv[++i]); }
+        else if (a == "--ellipse-ax") { need(1); prm.ell_ax = atof(argv[++i]); }
+        else if (a == "--rhs") { need(1); prm.rhs_mode = std::string(argv[++i]) == "area" ? PB200_RHS_AREA : PB200_RHS_INDICATOR; }
+        else if (a == "--report-error") report_error = true;
         else if (a == "--rect") { need(4); prm.A1 = atof(argv[++i]); prm.B1 = atof(argv[++i]); prm.A2 = atof(argv[++i]); prm.B2 = atof(argv[++i]); }
         else if (a == "--norm") { need(1); std::string v = argv[++i]; prm.norm_mode = (v == "stage0" || v == "unweighted") ? PB200_NORM_STAGE0 : PB200_NORM_WEIGHTED; }
         else if (a == "--gpus") { need(1); gpus = atoi(argv[++i]); }
@@ -209,16 +215,20 @@ int main(int argc, char **argv) {
     std::cout << "   Init time (program)      ~ " << time_init << " s\n";     // S4:1032
     std::cout << "   Solver time (MPI+CUDA)   ~ " << time_solver << " s\n";   // S4:1033
     std::cout << "   Finalization time        ~ " << time_finalize << " s\n"; // S4:1034
+    if (report_error) // not a line of the reference (it never compares with the analytic solution it states, R4 p.1-2): opt-in
+        std::cout << "   Error vs analytic solution in D: max = " << std::scientific << std::setprecision(6) << res.err_max_in_D
+                  << ", L2 = " << res.err_l2_in_D << "\n";
 
     if (!json.empty()) {
-        char buf[1024];
+        char buf[1536];
         snprintf(buf, sizeof(buf),
                  "{\"M\": %d, \"N\": %d, \"gpus\": %d, \"iterations\": %lld, \"stop_reason\": %d, \"first_converged_iter\": %d, "
                  "\"diff_norm\": %.17g, \"zr\": %.17g, \"w_norm_E\": %.17g, \"r_norm_E\": %.17g, \"w_max\": %.17g, "
+                 "\"err_max_in_D\": %.17g, \"err_l2_in_D\": %.17g, "
                  "\"t_setup_s\": %.6g, \"t_loop_s\": %.6g, \"t_solver_s\": %.6g, \"pt_it_per_s\": %.6g, \"algo_gbps\": %.6g, "
                  "\"kernel_launches\": %lld}\n",
                  M, N, gpus, (long long)res.iterations, res.stop_reason, res.first_converged_iter, res.diff_norm, res.zr,
-                 res.w_norm_E, res.r_norm_E, res.w_max, t_setup, t_loop, time_solver,
+                 res.w_norm_E, res.r_norm_E, res.w_max, res.err_max_in_D, res.err_l2_in_D, t_setup, t_loop, time_solver,
                  t_loop > 0 ? double(M - 1) * (N - 1) * res.iterations / t_loop : 0.0,
                  t_loop > 0 ? double(M - 1) * (N - 1) * res.iterations / t_loop * 104e-9 : 0.0, (long long)res.kernel_launches);
         if (json == "-") std::cerr << buf;

@@ -289,9 +289,9 @@ pb200_status Solver::reduce_norms_host(double *) {
         comm->async_err = ncclSuccess;
         return PB200_ERR_COMM;
     }
-    // in-stream: sums of w^2, r^2 and the max |w| (bit pattern of a non-negative double orders like uint64)
-    NK(nccl().AllReduce(norms, norms, 2, ncclDouble, ncclSum, comm->nc, stream));
-    NK(nccl().AllReduce(norms + 2, norms + 2, 1, ncclUint64, ncclMax, comm->nc, stream));
+    // in-stream: sums of w^2, r^2, (w-u)^2 and the maxima of |w|, |w-u| (bit pattern of a non-negative double orders like uint64)
+    NK(nccl().AllReduce(norms, norms, 3, ncclDouble, ncclSum, comm->nc, stream));
+    NK(nccl().AllReduce(norms + 3, norms + 3, 2, ncclUint64, ncclMax, comm->nc, stream));
     if (comm->async_err != ncclSuccess) {
         set_error("NCCL error during the loop: %s", nccl().GetErrorString(comm->async_err));
         return PB200_ERR_COMM;

@@ -52,7 +52,10 @@ struct Consts {
     int pow2;                  // bit 0: h1 is a power of two, bit 1: h2 is (x / h is then the exact product x * rh)
     double h1h1, h2h2;         // h1*h1, h2*h2 (S4:556-557)
     double eps, inv_eps;       // S4:693; 1.0/eps (S4:169)
-    double ell_k, ell_c;       // ellipse x^2 + (k y)^2 < 1; c = k*k (S4:33: 4.0)
+    double ell_k, ell_c;       // ellipse (x/ax)^2 + (k y)^2 < 1; c = k*k (S4:33: 4.0)
+    double ell_ax, inv_ax2;    // x semi-axis (the reference: 1) and 1/(ax*ax); with ax = 1 every product below is exact
+    int rhs_mode;              // 0: point indicator (S4:182-191); 1: area fraction of the cell (no reference counterpart)
+    double u_scale;            // f / (2/ax^2 + 2 k^2): the analytic solution on D is u_scale * (1 - (x/ax)^2 - (k y)^2)
     double f_val;              // S4:13
     double delta;              // S4:1006
     int norm_mode;             // 0 weighted (S4:897), 1 stage0 (S0:154)
@@ -234,31 +237,107 @@ __device__ __forceinline__ double seg_len(const Consts &c, double cc, double s, 
     double l;
     if (vertical) {
         const double x0 = cc;
-        if (fabs(x0) >= 1.0) l = 0.0; // S4:51
+        if (fabs(x0) >= c.ell_ax) l = 0.0; // S4:51
         else {
-            const double root = sqrt(dmax_std(0.0, (1.0 - x0 * x0) / c.ell_c)); // S4:53-54
-            l = dmax_std(0.0, dmin_std(e, root) - dmax_std(s, -root));          // S4:55
+            const double root = sqrt(dmax_std(0.0, (1.0 - x0 * x0 * c.inv_ax2) / c.ell_c)); // S4:53-54
+            l = dmax_std(0.0, dmin_std(e, root) - dmax_std(s, -root));                      // S4:55
         }
     } else {
         const double y0 = cc;
         if (fabs(c.ell_k * y0) >= 1.0) l = 0.0; // S4:59
         else {
-            const double root = sqrt(dmax_std(0.0, 1.0 - c.ell_c * y0 * y0)); // S4:61-62
-            l = dmax_std(0.0, dmin_std(e, root) - dmax_std(s, -root));        // S4:63
+            const double root = c.ell_ax * sqrt(dmax_std(0.0, 1.0 - c.ell_c * y0 * y0)); // S4:61-62
+            l = dmax_std(0.0, dmin_std(e, root) - dmax_std(s, -root));                   // S4:63
         }
     }
     return l;
 }
 
-__device__ __forceinline__ double coef_a(const Consts &c, int gi, int gj) { // S4:159-163, 167-171
+// length inside D of the vertical edge left of node (gi,gj) / of the horizontal edge below it (S4:159-165)
+__device__ __forceinline__ double len_a(const Consts &c, int gi, int gj) {
     const double x = c.A1 + gi * c.h1, y = c.A2 + gj * c.h2;
-    const double l = seg_len(c, x - 0.5 * c.h1, y - 0.5 * c.h2, y + 0.5 * c.h2, true);
-    return (fabs(l - c.h2) < 1e-9) ? 1.0 : (l < 1e-9 ? 1.0 / c.eps : (l / c.h2) + (1.0 - l / c.h2) / c.eps);
+    return seg_len(c, x - 0.5 * c.h1, y - 0.5 * c.h2, y + 0.5 * c.h2, true);
 }
-__device__ __forceinline__ double coef_b(const Consts &c, int gi, int gj) { // S4:159-160, 164-165, 173-177
+__device__ __forceinline__ double len_b(const Consts &c, int gi, int gj) {
     const double x = c.A1 + gi * c.h1, y = c.A2 + gj * c.h2;
-    const double l = seg_len(c, y - 0.5 * c.h2, x - 0.5 * c.h1, x + 0.5 * c.h1, false);
-    return (fabs(l - c.h1) < 1e-9) ? 1.0 : (l < 1e-9 ? 1.0 / c.eps : (l / c.h1) + (1.0 - l / c.h1) / c.eps);
+    return seg_len(c, y - 0.5 * c.h2, x - 0.5 * c.h1, x + 0.5 * c.h1, false);
+}
+// S4:167-171 / 173-177: the coefficient of an edge of length h of which l lies inside D
+__device__ __forceinline__ double coef_of(const Consts &c, double l, double h) {
+    return (fabs(l - h) < 1e-9) ? 1.0 : (l < 1e-9 ? 1.0 / c.eps : (l / h) + (1.0 - l / h) / c.eps);
+}
+__device__ __forceinline__ double coef_a(const Consts &c, int gi, int gj) { return coef_of(c, len_a(c, gi, gj), c.h2); }
+__device__ __forceinline__ double coef_b(const Consts &c, int gi, int gj) { return coef_of(c, len_b(c, gi, gj), c.h1); }
+
+// S4:32-34
+__device__ __forceinline__ bool in_D(const Consts &c, double x, double y) { return x * x * c.inv_ax2 + c.ell_c * y * y < 1.0; }
+
+// The part [lo, hi] of a cell edge that lies in D: the two clamped end points whose difference seg_len returns
+// (S4:46-76, same expressions). False when the edge misses D.
+__device__ __forceinline__ bool seg_ends(const Consts &c, double cc, double s, double e, bool vertical, double &lo, double &hi) {
+    double root;
+    if (vertical) {
+        if (fabs(cc) >= c.ell_ax) return false;                                // S4:51
+        root = sqrt(dmax_std(0.0, (1.0 - cc * cc * c.inv_ax2) / c.ell_c));     // S4:53-54
+    } else {
+        if (fabs(c.ell_k * cc) >= 1.0) return false;                           // S4:59
+        root = c.ell_ax * sqrt(dmax_std(0.0, 1.0 - c.ell_c * cc * cc));        // S4:61-62
+    }
+    lo = dmax_std(s, -root); // S4:55, 63
+    hi = dmin_std(e, root);
+    return hi > lo;
+}
+
+// running shoelace sum over the vertices of a polygon given in order
+struct Shoelace {
+    int n = 0;
+    double x0 = 0.0, y0 = 0.0, xp = 0.0, yp = 0.0, sum = 0.0;
+    __device__ __forceinline__ void add(double x, double y) {
+        if (n == 0) {
+            x0 = x;
+            y0 = y;
+        } else
+            sum += xp * y - x * yp;
+        xp = x;
+        yp = y;
+        ++n;
+    }
+};
+
+// Right-hand side of node (gi,gj). Mode 0 is the reference's point indicator (S4:182-191). Mode 1 (north_star's "area
+// fractions", not in the reference) weighs f by the share of the node's cell [x_i-h1/2, x_{i+1}-h1/2] x [y_j-h2/2,
+// y_{j+1}-h2/2] that lies in D: the area of the polygon whose vertices are the end points of the in-D parts of the cell's
+// four edges -- the edge intersections S4:46-76 computes for a and b -- walked counter-clockwise in coordinates relative
+// to the node (the cell clipped by the chords of the ellipse, second-order accurate), snapped to 0 / 1 with the
+// reference's 1e-9 threshold so that cells wholly inside get exactly f.
+__device__ __forceinline__ double rhs_value(const Consts &c, int gi, int gj) {
+    const double x_i = c.A1 + gi * c.h1, y_j = c.A2 + gj * c.h2; // S4:159-160
+    if (c.rhs_mode == 0) return in_D(c, x_i, y_j) ? c.f_val : 0.0; // S4:189
+    const double x_ip = c.A1 + (gi + 1) * c.h1, y_jp = c.A2 + (gj + 1) * c.h2;
+    const double xl = x_i - 0.5 * c.h1, xr = x_ip - 0.5 * c.h1, yb = y_j - 0.5 * c.h2, yt = y_jp - 0.5 * c.h2;
+    double lo, hi;
+    Shoelace q;
+    if (seg_ends(c, yb, xl, xr, false, lo, hi)) { // bottom edge, left to right
+        q.add(lo - x_i, yb - y_j);
+        q.add(hi - x_i, yb - y_j);
+    }
+    if (seg_ends(c, xr, yb, yt, true, lo, hi)) { // right edge, upwards
+        q.add(xr - x_i, lo - y_j);
+        q.add(xr - x_i, hi - y_j);
+    }
+    if (seg_ends(c, yt, xl, xr, false, lo, hi)) { // top edge, right to left
+        q.add(hi - x_i, yt - y_j);
+        q.add(lo - x_i, yt - y_j);
+    }
+    if (seg_ends(c, xl, yb, yt, true, lo, hi)) { // left edge, downwards
+        q.add(xl - x_i, hi - y_j);
+        q.add(xl - x_i, lo - y_j);
+    }
+    if (q.n == 0) return 0.0;
+    q.sum += q.xp * q.y0 - q.x0 * q.yp;
+    double frac = (0.5 * q.sum) / (c.h1 * c.h2);
+    frac = (fabs(frac - 1.0) < 1e-9) ? 1.0 : (frac < 1e-9 ? 0.0 : frac);
+    return c.f_val * frac;
 }
 
 // One thread per stored cell (ring and padding included). Writes a, b (block + ring, S4:154-179),
@@ -278,14 +357,15 @@ __global__ void __launch_bounds__(256) setup_kernel(Geom g, Consts c, double *__
     unsigned vc = CLS_GENERAL | (CLS_GENERAL << 2) | (DCLS_RING << 4);
     if (lj <= g.ny + 1) {
         const int gi = g.gi0 + li, gj = g.gj0 + lj;
-        va = coef_a(c, gi, gj);
-        vb = coef_b(c, gi, gj);
+        const double la = len_a(c, gi, gj), lb = len_b(c, gi, gj);
+        va = coef_of(c, la, c.h2);
+        vb = coef_of(c, lb, c.h1);
         const unsigned ca = coef_class(va, c.inv_eps), cb = coef_class(vb, c.inv_eps);
         unsigned cD = DCLS_RING;
         if (gi >= 1 && gi <= g.M - 1 && gj >= 1 && gj <= g.N - 1) {
-            const double x = c.A1 + gi * c.h1, y = c.A2 + gj * c.h2;
-            vr = (x * x + c.ell_c * y * y < 1.0) ? c.f_val : 0.0; // S4:32-34, 189
-            const double a_ip = coef_a(c, gi + 1, gj), b_jp = coef_b(c, gi, gj + 1);
+            const double la_ip = len_a(c, gi + 1, gj), lb_jp = len_b(c, gi, gj + 1);
+            vr = rhs_value(c, gi, gj); // S4:32-34, 189
+            const double a_ip = coef_of(c, la_ip, c.h2), b_jp = coef_of(c, lb_jp, c.h1);
             vD = (a_ip + va) / c.h1h1 + (b_jp + vb) / c.h2h2; // S4:556-557
             cD = diag_class(c, coef_class(a_ip, c.inv_eps), ca, coef_class(b_jp, c.inv_eps), cb, vD);
         }
@@ -1552,34 +1632,56 @@ __global__ void finalize_kernel(Ctl *ctl, Consts c, double *trace, int init) {
 }
 
 // ------------------------------------------------------------------------------------------
-// norms of the result (reporting only): sum w^2, sum r^2, max |w| over the interior.
-__global__ void __launch_bounds__(256) norms_kernel(Geom g, const double *__restrict__ w, const double *__restrict__ r,
-                                                    double *partials, unsigned int *ticket, double *out3) {
-    __shared__ double s_max[8];
-    double acc[2] = {0.0, 0.0};
-    double mx = 0.0;
+// norms of the result (reporting only): sum w^2, sum r^2, max |w| over the interior, and the distance to the analytic
+// solution u = f (1 - (x/ax)^2 - (k y)^2) / (2/ax^2 + 2 k^2) of the problem on D (R4 p.1-2: u = (1 - x^2 - 4y^2)/10) over the
+// nodes inside D: sum (w-u)^2 and max |w-u|. The reference states u but frees w unseen (S4:946-954).
+// out5 = { sum w^2, sum r^2, sum (w-u)^2 | max |w|, max |w-u| }: the first three add over ranks, the last two take the max.
+__global__ void __launch_bounds__(256) norms_kernel(Geom g, Consts c, const double *__restrict__ w, const double *__restrict__ r,
+                                                    double *partials, unsigned int *ticket, double *out5) {
+    __shared__ double s_max[2][8];
+    double acc[3] = {0.0, 0.0, 0.0};
+    double mx = 0.0, ex = 0.0;
     const int lj = 1 + blockIdx.x * blockDim.x + threadIdx.x;
-    if (lj <= g.ny)
+    if (lj <= g.ny) {
+        const double y = c.A2 + (g.gj0 + lj) * c.h2; // S4:160
         for (int li = 1 + blockIdx.y; li <= g.nx; li += gridDim.y) {
             const size_t o = (size_t)li * g.pitch + lj;
             const double vw = w[o], vr = r[o];
             acc[0] += vw * vw;
             acc[1] += vr * vr;
             mx = fmax(mx, fabs(vw));
+            const double x = c.A1 + (g.gi0 + li) * c.h1; // S4:159
+            if (in_D(c, x, y)) {
+                const double e = fabs(vw - c.u_scale * (1.0 - x * x * c.inv_ax2 - c.ell_c * y * y));
+                acc[2] += e * e;
+                ex = fmax(ex, e);
+            }
         }
-    // block maximum, then ONE atomic per block (bit pattern of a non-negative double orders like an integer)
+    }
+    // block maxima, then ONE atomic per block and value (bit pattern of a non-negative double orders like an integer)
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmax(mx, __shfl_down_sync(0xffffffffu, mx, o));
-    if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = mx;
+    for (int o = 16; o > 0; o >>= 1) {
+        mx = fmax(mx, __shfl_down_sync(0xffffffffu, mx, o));
+        ex = fmax(ex, __shfl_down_sync(0xffffffffu, ex, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        s_max[0][threadIdx.x >> 5] = mx;
+        s_max[1][threadIdx.x >> 5] = ex;
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
-        for (int k = 1; k < 8; ++k) mx = fmax(mx, s_max[k]);
-        atomicMax(reinterpret_cast<unsigned long long *>(&out3[2]), (unsigned long long)__double_as_longlong(mx));
+        for (int k = 1; k < 8; ++k) {
+            mx = fmax(mx, s_max[0][k]);
+            ex = fmax(ex, s_max[1][k]);
+        }
+        atomicMax(reinterpret_cast<unsigned long long *>(&out5[3]), (unsigned long long)__double_as_longlong(mx));
+        atomicMax(reinterpret_cast<unsigned long long *>(&out5[4]), (unsigned long long)__double_as_longlong(ex));
     }
-    double tot[2];
-    if (grid_reduce<2, 256>(acc, partials, ticket, tot)) {
-        out3[0] = tot[0];
-        out3[1] = tot[1];
+    double tot[3];
+    if (grid_reduce<3, 256>(acc, partials, ticket, tot)) {
+        out5[0] = tot[0];
+        out5[1] = tot[1];
+        out5[2] = tot[2];
     }
 }
 
@@ -1593,8 +1695,7 @@ __global__ void __launch_bounds__(256) reset_kernel(Geom g, Consts c, double *__
     double vr = 0.0;
     const int gi = g.gi0 + li, gj = g.gj0 + lj;
     if (lj <= g.ny + 1 && gi >= 1 && gi <= g.M - 1 && gj >= 1 && gj <= g.N - 1) {
-        const double x = c.A1 + gi * c.h1, y = c.A2 + gj * c.h2;
-        vr = (x * x + c.ell_c * y * y < 1.0) ? c.f_val : 0.0; // S4:32-34, 189
+        vr = rhs_value(c, gi, gj); // S4:32-34, 189
     }
     r[o] = vr;
     w[o] = 0.0;

@@ -58,6 +58,8 @@ pb200_status validate(const pb200_params &p) {
     if (p.M < 2 || p.N < 2) { set_error("M and N must be >= 2 (got %d, %d)", p.M, p.N); return PB200_ERR_INVALID; }
     if (!(p.B1 > p.A1) || !(p.B2 > p.A2)) { set_error("empty rectangle"); return PB200_ERR_INVALID; }
     if (!(p.ell_k > 0.0)) { set_error("ell_k must be > 0"); return PB200_ERR_INVALID; }
+    if (p.ell_ax < 0.0 || p.ell_ax != p.ell_ax) { set_error("ell_ax must be > 0 (or 0 for the reference's 1)"); return PB200_ERR_INVALID; }
+    if (p.rhs_mode != PB200_RHS_INDICATOR && p.rhs_mode != PB200_RHS_AREA) { set_error("bad rhs_mode"); return PB200_ERR_INVALID; }
     if (!(p.delta >= 0.0)) { set_error("delta must be >= 0"); return PB200_ERR_INVALID; }
     if (p.norm_mode != PB200_NORM_WEIGHTED && p.norm_mode != PB200_NORM_STAGE0) { set_error("bad norm_mode"); return PB200_ERR_INVALID; }
     if (p.nranks < 1 || p.rank < 0 || p.rank >= p.nranks) { set_error("bad rank %d of %d", p.rank, p.nranks); return PB200_ERR_INVALID; }
@@ -85,6 +87,10 @@ Consts make_consts(const pb200_params &p) {
     c.inv_eps = 1.0 / c.eps;
     c.ell_k = p.ell_k;
     c.ell_c = p.ell_k * p.ell_k;
+    c.ell_ax = p.ell_ax > 0.0 ? p.ell_ax : 1.0; // S4:32-34: the reference's ellipse has x semi-axis 1
+    c.inv_ax2 = 1.0 / (c.ell_ax * c.ell_ax);
+    c.rhs_mode = p.rhs_mode;
+    c.u_scale = p.f_val / (2.0 * c.inv_ax2 + 2.0 * c.ell_c); // -laplace(u) = f for u = u_scale (1 - (x/ax)^2 - (k y)^2)
     c.f_val = p.f_val;
     c.delta = p.delta;
     c.norm_mode = p.norm_mode;
@@ -336,8 +342,8 @@ pb200_status Solver::create(const pb200_params &params) {
     CK(cudaMalloc(&ctl, sizeof(Ctl)));
     CK(cudaMalloc(&part1, nb1 * sizeof(double)));
     const size_t nb3 = std::max(static_cast<size_t>(norms_grid.x) * norms_grid.y, static_cast<size_t>(init_grid.x) * init_grid.y);
-    CK(cudaMalloc(&part2, 2 * std::max(nb2, nb3) * sizeof(double)));
-    CK(cudaMalloc(&norms, 4 * sizeof(double)));
+    CK(cudaMalloc(&part2, std::max(2 * nb2, 3 * nb3) * sizeof(double))); // norms_kernel: 3 partials per block
+    CK(cudaMalloc(&norms, 8 * sizeof(double)));
     if (c.trace_len > 0) {
         CK(cudaMalloc(&trace, static_cast<size_t>(c.trace_len) * 3 * sizeof(double)));
         CK(cudaMemsetAsync(trace, 0, static_cast<size_t>(c.trace_len) * 3 * sizeof(double), stream));
@@ -456,7 +462,7 @@ pb200_status Solver::solve(pb200_result *res) {
     }
     // ---- init (S4:803-843): w = 0 and r = B were written by setup; zr_old = (D^-1 r, r)
     CK(cudaMemsetAsync(ctl, 0, sizeof(Ctl), stream));
-    CK(cudaMemsetAsync(norms, 0, 4 * sizeof(double), stream));
+    CK(cudaMemsetAsync(norms, 0, 8 * sizeof(double), stream));
     // peer-memory mode: clear the mailbox; the NCCL all-reduce of the start-up (z,r) below doubles as the barrier that
     // keeps any rank from posting into a mailbox that has not been cleared yet
     if (c.multi == 2) CK(cudaMemsetAsync(mail, 0, MAIL_DOUBLES * sizeof(double), stream));
@@ -560,16 +566,16 @@ pb200_status Solver::solve(pb200_result *res) {
     CK(cudaGetLastError());
     // ---- results
     {
-        norms_kernel<<<norms_grid, 256, 0, stream>>>(f.g, f.w, f.r, part2, &ctl->ticket[1], norms);
+        norms_kernel<<<norms_grid, 256, 0, stream>>>(f.g, c, f.w, f.r, part2, &ctl->ticket[1], norms);
         ++launches;
     }
-    double h_norms[4] = {0, 0, 0, 0};
+    double h_norms[5] = {0, 0, 0, 0, 0}; // sum w^2, sum r^2, sum (w-u)^2 in D | max |w|, max |w-u| in D
     if (c.multi) { // sums and max over all ranks, in stream
         pb200_status st = reduce_norms_host(h_norms);
         if (st != PB200_OK) return st;
     }
     CK(cudaMemcpyAsync(&h_ctl[0], ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, stream));
-    CK(cudaMemcpyAsync(h_norms, norms, 3 * sizeof(double), cudaMemcpyDeviceToHost, stream));
+    CK(cudaMemcpyAsync(h_norms, norms, 5 * sizeof(double), cudaMemcpyDeviceToHost, stream));
     CK(cudaEventRecord(ev_call1, stream));
     CK(cudaStreamSynchronize(stream));
     CK(cudaGetLastError());
@@ -591,7 +597,9 @@ pb200_status Solver::solve(pb200_result *res) {
         res->beta = hc.beta;
         res->w_norm_E = std::sqrt(h_norms[0] * c.h1 * c.h2);
         res->r_norm_E = std::sqrt(h_norms[1] * c.h1 * c.h2);
-        res->w_max = h_norms[2];
+        res->w_max = h_norms[3];
+        res->err_max_in_D = h_norms[4];
+        res->err_l2_in_D = std::sqrt(h_norms[2] * c.h1 * c.h2);
         res->t_setup_s = t_setup;
         res->t_solve_s = ms * 1e-3;
         res->t_total_s = now_s() - t0;

@@ -21,7 +21,8 @@ class Problem(C.Structure):
     """po_problem (oracle/poisson_oracle.h)."""
 
     _fields_ = [("A1", C.c_double), ("B1", C.c_double), ("A2", C.c_double), ("B2", C.c_double),
-                ("f_val", C.c_double), ("ell_k", C.c_double), ("eps", C.c_double)]
+                ("f_val", C.c_double), ("ell_k", C.c_double), ("eps", C.c_double), ("ell_ax", C.c_double),
+                ("rhs_mode", C.c_int)]
 
 
 class Result(C.Structure):
@@ -30,7 +31,7 @@ class Result(C.Structure):
     _fields_ = [("iterations", C.c_int), ("converged", C.c_int), ("denom_break", C.c_int),
                 ("diff_norm", C.c_double), ("zr", C.c_double), ("alpha", C.c_double),
                 ("w_norm_E", C.c_double), ("r_norm_E", C.c_double), ("w_max", C.c_double),
-                ("err_max_in_D", C.c_double)]
+                ("err_max_in_D", C.c_double), ("err_l2_in_D", C.c_double)]
 
 
 def _ptr(arr):

@@ -18,7 +18,7 @@ def test_exports_match_header():
     lib = pb.lib()
     for s in declared:
         assert hasattr(lib, s), s
-    assert lib.pb200_api_version() == 1
+    assert lib.pb200_api_version() == 2
 
 
 def test_default_params_are_the_reference_constants():
@@ -26,6 +26,9 @@ def test_default_params_are_the_reference_constants():
     assert (p.M, p.N, p.delta, p.max_iter) == (40, 40, 1e-6, 0)          # S4:996-1007
     assert (p.A1, p.B1, p.A2, p.B2, p.f_val, p.ell_k) == (-1.0, 1.0, -0.6, 0.6, 1.0, 2.0)  # S4:11-13, 33
     assert p.norm_mode == pb.NORM_WEIGHTED and p.nranks == 1
+    assert p.ell_ax == 1.0 and p.rhs_mode == pb.RHS_INDICATOR          # S4:32-34, 182-191
+    import ctypes
+    assert ctypes.sizeof(pb.Params) == 152 and ctypes.sizeof(pb.Result) == 168          # the v1 layout, reserved words reused
 
 
 def test_process_grid_and_decomposition(golden):

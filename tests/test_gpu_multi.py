@@ -44,6 +44,17 @@ def test_cli_single_gpu_report_lines(tmp_path, golden):
     assert lines[9].startswith("   Solver time (MPI+CUDA)   ~ ")
     assert lines[10].startswith("   Finalization time        ~ ")
     assert res["iterations"] == golden["iters_stage3"]["40x40"] and w.shape == (41, 41)
+    assert len(lines) == 11          # nothing but the reference's lines unless asked
+    assert res["err_max_in_D"] == pytest.approx(6.418e-3, rel=1e-3) and 0 < res["err_l2_in_D"] < res["err_max_in_D"] * 2
+
+
+def test_cli_report_error_and_geometry_flags(tmp_path):
+    """--report-error appends one line after the reference's; --ellipse-ax / --rhs reach the solver."""
+    out, res, _ = run_cli(tmp_path, 40, 40, 1, ("--report-error",))
+    lines = out.splitlines()
+    assert len(lines) == 12 and lines[11].startswith("   Error vs analytic solution in D: max = 6.41")
+    _, res2, _ = run_cli(tmp_path, 40, 40, 1, ("--ellipse-ax", "0.8", "--rhs", "area"))
+    assert res2["w_norm_E"] != res["w_norm_E"] and res2["iterations"] > 0
 
 
 @pytest.mark.parametrize("M,N,gpus,extra", [(40, 40, 2, ()), (400, 600, 2, ()), (400, 600, 2, ("--grid", "2x1")),

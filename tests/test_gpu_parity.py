@@ -87,6 +87,53 @@ def test_setup_other_ellipse_and_eps(oracle):
     assert np.array_equal(a, oa) and np.array_equal(b, ob) and np.array_equal(B, oB)
 
 
+@pytest.mark.parametrize("m,n,kw,blk", [(48, 36, dict(ell_ax=0.8, ell_k=2.5), None),
+                                        (64, 50, dict(rhs_mode=1), None),
+                                        (130, 97, dict(ell_ax=0.55, ell_k=1.9, rhs_mode=1, f_val=2.5), None),
+                                        (400, 600, dict(ell_ax=0.9, rhs_mode=1), (201, 400, 151, 300)),
+                                        (1024, 512, dict(rhs_mode=1), (1, 200, 300, 511))])
+def test_setup_generalised_geometry_bit_exact(oracle, m, n, kw, blk):
+    """a second free semi-axis and the area-fraction right-hand side. Neither exists in the
+    reference; the oracle restates them with the same operations in the same order, so the device arrays are
+    bit-identical -- on whole grids and on a block of a decomposition (ring from global indices)."""
+    okw = dict(kw)
+    prm = pb.default_params(m, n, **kw)
+    a, b, B, D = pb.op_setup(prm, blk)
+    oa, ob, oB = oracle.setup(m, n, blk, pb=oracle.problem(**okw))
+    assert np.array_equal(a, oa) and np.array_equal(b, ob) and np.array_equal(B, oB)
+    if kw.get("rhs_mode"):
+        f = kw.get("f_val", 1.0)
+        cut = (B > 0) & (B < f)
+        assert cut.any() and B.max() == f          # cells cut by the ellipse carry a fraction, whole cells exactly f
+
+
+@pytest.mark.parametrize("m,n,kw", [(96, 72, dict(ell_ax=0.8, ell_k=2.5)), (120, 90, dict(rhs_mode=1)),
+                                    (400, 600, dict(rhs_mode=1)), (100, 140, dict(ell_ax=0.6, rhs_mode=1, f_val=3.0))])
+def test_solve_generalised_geometry(oracle, monkeypatch, m, n, kw):
+    for loop in ("1", "0"):          # the resident loop kernel and the two marching kernels
+        monkeypatch.setenv("PB200_LOOP", loop)
+        pb.release_cache()
+        res, w = pb.run(pb.default_params(m, n, **kw), want_w=True)
+        ores, ow, _ = oracle.solve(m, n, pb=oracle.problem(**kw), want_w=True)
+        assert res.iterations == ores.iterations and res.stop_reason == pb.STOP_CONVERGED
+        assert rel(res.w_norm_E, ores.w_norm_E) < RTOL_NORM and rel(res.diff_norm, ores.diff_norm) < RTOL_NORM
+        np.testing.assert_allclose(w, ow, rtol=0, atol=1e-11)
+        assert rel(res.err_max_in_D, ores.err_max_in_D) < 1e-8 and rel(res.err_l2_in_D, ores.err_l2_in_D) < 1e-8
+    pb.release_cache()
+
+
+@pytest.mark.parametrize("m,n,want", [(40, 40, 6.418e-3), (400, 600, 6.216e-4)])
+def test_analytic_error_in_result(oracle, m, n, want):
+    """max |w - (1 - x^2 - 4y^2)/10| over the nodes in D, as measured on the reference (6.418e-3 at
+    40 x 40, 6.216e-4 at 400 x 600), reported by the solver itself together with the L2 error."""
+    res, _ = pb.run(pb.default_params(m, n))
+    ores, _, _ = oracle.solve(m, n)
+    assert res.err_max_in_D == pytest.approx(want, rel=1e-3)
+    assert rel(res.err_max_in_D, ores.err_max_in_D) < 1e-8
+    assert rel(res.err_l2_in_D, ores.err_l2_in_D) < 1e-8
+    assert 0 < res.err_l2_in_D < res.err_max_in_D * 2.0          # |D| = pi/2
+
+
 # --------------------------------------------------------------------------------------------
 # operators on seeded inputs; shapes chosen to hit every edge of the kernel's tiling
 # (124-column warp windows of 4-column lanes, 4-warp CTAs = 496 columns, 3-row pieces in these entry points,

@@ -140,3 +140,72 @@ def test_against_live_reference(oracle, reference):
         assert np.array_equal(oracle.apply_Dinv(p, a, b, h1, h2), reference.apply_Dinv(p, a, b, h1, h2))
     assert oracle.solve(m, n)[0].iterations == reference.solve(m, n)
     assert oracle.solve(m, n, norm_mode=1)[0].iterations == reference.solve_stage0(m, n)
+
+
+# --------------------------------------------------------------------------------------------
+# Extensions beyond the reference: the oracle is the definition here, so it is checked against
+# independent mathematics rather than against reference outputs.
+
+def test_analytic_error_report(oracle):
+    """max |w - u| inside D against u = (1 - x^2 - 4y^2)/10 (R4 p.1-2): 6.418e-3 at 40 x 40 (measured on the
+    reference), recomputed here from the solution array."""
+    m = n = 40
+    res, w, _ = oracle.solve(m, n, want_w=True)
+    x = -1.0 + np.arange(m + 1) * (2.0 / m)
+    y = -0.6 + np.arange(n + 1) * (1.2 / n)
+    X, Y = np.meshgrid(x, y, indexing="ij")
+    inside = (X * X + 4 * Y * Y < 1)
+    inside[0, :] = inside[-1, :] = False
+    inside[:, 0] = inside[:, -1] = False
+    e = np.abs(w - (1 - X * X - 4 * Y * Y) / 10)[inside]
+    assert res.err_max_in_D == pytest.approx(6.418e-3, rel=1e-3)
+    assert res.err_max_in_D == pytest.approx(e.max(), rel=1e-12)
+    assert res.err_l2_in_D == pytest.approx(np.sqrt((e * e).sum() * (2.0 / m) * (1.2 / n)), rel=1e-12)
+
+
+@pytest.mark.parametrize("ax,k", [(1.0, 2.0), (0.8, 2.5), (0.55, 1.9)])
+def test_area_fraction_rhs(oracle, ax, k):
+    """rhs_mode 1: f times the share of each node's cell inside the ellipse. Cells wholly inside get exactly f, cells
+    wholly outside exactly 0, cut cells agree with a 64 x 64 sub-sampling of the cell to a few per cent of a cell, and
+    the sum times h1*h2 approaches f * pi * ax / k (the ellipse's area) at second order."""
+    f = 2.5
+    errs = []
+    for m, n in ((40, 40), (80, 80)):
+        pbm = oracle.problem(ell_ax=ax, ell_k=k, f_val=f, rhs_mode=1)
+        _, _, B = oracle.setup(m, n, pb=pbm)
+        _, _, Bi = oracle.setup(m, n, pb=oracle.problem(ell_ax=ax, ell_k=k, f_val=f))
+        h1, h2 = 2.0 / m, 1.2 / n
+        x = -1.0 + np.arange(m + 1) * h1
+        y = -0.6 + np.arange(n + 1) * h2
+        sub = (np.arange(64) + 0.5) / 64 - 0.5
+        worst = 0.0
+        for i in range(1, m):
+            for j in range(1, n):
+                xs, ys = x[i] + sub * h1, y[j] + sub * h2
+                XX, YY = np.meshgrid(xs, ys, indexing="ij")
+                frac = ((XX / ax) ** 2 + (k * YY) ** 2 < 1).mean()
+                got = B[i, j] / f
+                corners = [((x[i] + sx * h1 / 2) / ax) ** 2 + (k * (y[j] + sy * h2 / 2)) ** 2 for sx in (-1, 1) for sy in (-1, 1)]
+                if max(corners) < 1 - 1e-6:          # D is convex: all four corners inside = the whole cell inside
+                    assert B[i, j] == f, (i, j)
+                elif frac == 0.0 and got != 0.0:          # an edge may clip a corner the sampling missed
+                    assert got < 0.02, (i, j, got)
+                worst = max(worst, abs(got - frac))
+        assert worst < 0.06, worst          # trapezoid rule on a curved boundary: O(curvature * h) of a cell
+        area = B[1:-1, 1:-1].sum() * h1 * h2
+        errs.append(abs(area - f * np.pi * ax / k))
+        assert errs[-1] < 0.02 * f * np.pi * ax / k
+        assert not np.array_equal(B, Bi)          # it is not the indicator
+    assert errs[1] < 0.6 * errs[0]          # refines
+
+
+def test_other_semi_axis_solve_matches_its_analytic_solution(oracle):
+    """A second free semi-axis: (x/ax)^2 + (k y)^2 < 1. The solve converges and its distance to the analytic solution
+    u = f (1 - (x/ax)^2 - (k y)^2) / (2/ax^2 + 2 k^2) is of the size the fictitious-domain method gives on the reference's
+    own ellipse at the same resolution."""
+    ref, _, _ = oracle.solve(80, 80)
+    res, _, _ = oracle.solve(80, 80, pb=oracle.problem(ell_ax=0.8, ell_k=2.5))
+    assert res.converged == 1 and ref.converged == 1
+    assert res.err_max_in_D < 3 * ref.err_max_in_D and res.err_max_in_D > 0
+    area, _, _ = oracle.solve(80, 80, pb=oracle.problem(rhs_mode=1))
+    assert area.converged == 1 and area.err_max_in_D < 3 * ref.err_max_in_D

@@ -38,7 +38,7 @@ def noalloc_dot(torch, u, v, nx, ny, h1, h2, stream=None):
     return float(out.item())
 
 
-def test_two_calls_in_a_row_match_the_allocating_entry_point():
+def test_two_calls_in_a_row_match_the_allocating_entry_point(oracle):
     import torch
     for nx, ny, seed in [(300, 513, 1), (300, 513, 2), (39, 39, 3), (1000, 64, 4)]:
         h1, h2 = 2.0 / (nx + 1), 1.2 / (ny + 1)
@@ -46,6 +46,8 @@ def test_two_calls_in_a_row_match_the_allocating_entry_point():
         want = pb.op_dot(pb.default_params(nx + 1, ny + 1), u, v)
         got = noalloc_dot(torch, u, v, nx, ny, h1, h2)
         assert abs(got - want) <= RTOL_DOT * abs(want), (nx, ny, seed, got, want)
+        cpu = oracle.dot(u, v, h1, h2)          # and against the CPU oracle directly, not only via pb200_op_dot
+        assert abs(got - cpu) <= RTOL_DOT * abs(cpu), (nx, ny, seed, got, cpu)
 
 
 def test_same_scratch_on_another_stream_after_the_first_call():
