@@ -90,7 +90,7 @@ def test_setup_other_ellipse_and_eps(oracle):
 @pytest.mark.parametrize("m,n,kw,blk", [(48, 36, dict(ell_ax=0.8, ell_k=2.5), None),
                                         (64, 50, dict(rhs_mode=1), None),
                                         (130, 97, dict(ell_ax=0.55, ell_k=1.9, rhs_mode=1, f_val=2.5), None),
-                                        (400, 600, dict(ell_ax=0.9, rhs_mode=1), (201, 400, 151, 300)),
+                                        (400, 600, dict(ell_ax=0.9, rhs_mode=1), (201, 399, 151, 300)),
                                         (1024, 512, dict(rhs_mode=1), (1, 200, 300, 511))])
 def test_setup_generalised_geometry_bit_exact(oracle, m, n, kw, blk):
     """a second free semi-axis and the area-fraction right-hand side. Neither exists in the
