@@ -137,6 +137,13 @@ pb200_status pb200_decompose_2d(int32_t M, int32_t N, int32_t Px, int32_t Py, in
  * split the rest the same way. Needs no GPU; used by the CPU tests to check that every row is covered once. */
 pb200_status pb200_launch_plan(int32_t nx, int32_t ny, int32_t resident_ctas, int32_t plan[6]);
 
+/* Host-only introspection, no reference counterpart: how the resident loop kernel (one cooperative launch for the whole
+ * solve, the block's state in shared memory) would cut a block of nx x ny cells into tiles for `sms` CTAs with
+ * `smem_bytes` of shared memory each (148 and 231000 on a B200): plan = { tile rows R, tile columns C, tiles down tr, tiles
+ * across tc }; tile (ti, tj) holds rows 1+ti*R .. min(nx,(ti+1)*R) and columns 1+tj*C .. min(ny,(tj+1)*C).
+ * PB200_ERR_TOO_LARGE: the block does not fit (it runs the two marching kernels instead). */
+pb200_status pb200_tile_plan(int32_t nx, int32_t ny, int32_t sms, int64_t smem_bytes, int32_t plan[4]);
+
 /* ---- the solver (replaces gradient_solver_mpi, S4:688-983) ---------------------------- */
 /* Allocates the block on the device and runs the coefficient/RHS kernel
  * (replaces fictitious_regions_setup_local S4:146-192 + flatten/upload S4:723-760). */

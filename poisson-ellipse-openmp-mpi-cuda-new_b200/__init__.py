@@ -57,7 +57,7 @@ class PB200Error(RuntimeError):
 
 # every symbol include/poisson_b200.h declares
 EXPORTS = ["pb200_api_version", "pb200_status_string", "pb200_last_error", "pb200_device_count",
-           "pb200_default_params", "pb200_choose_process_grid", "pb200_decompose_2d", "pb200_launch_plan", "pb200_create",
+           "pb200_default_params", "pb200_choose_process_grid", "pb200_decompose_2d", "pb200_launch_plan", "pb200_tile_plan", "pb200_create",
            "pb200_comm_unique_id", "pb200_attach_comm", "pb200_peer_export", "pb200_peer_attach", "pb200_solve", "pb200_get_solution", "pb200_get_trace",
            "pb200_get_field", "pb200_profile_iteration", "pb200_destroy", "pb200_run", "pb200_release_cache", "pb200_op_setup", "pb200_op_apply_A",
            "pb200_op_apply_Dinv", "pb200_op_iteration", "pb200_op_dot", "pb200_dot_noalloc", "pb200_selftest_div"]
@@ -80,6 +80,7 @@ def lib():
         L.pb200_choose_process_grid.argtypes = [C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
         L.pb200_decompose_2d.argtypes = [C.c_int32] * 5 + [C.POINTER(C.c_int32)] * 4
         L.pb200_launch_plan.argtypes = [C.c_int32] * 3 + [C.POINTER(C.c_int32)]
+        L.pb200_tile_plan.argtypes = [C.c_int32] * 3 + [C.c_int64, C.POINTER(C.c_int32)]
         L.pb200_create.argtypes = [C.POINTER(Params), C.POINTER(C.c_void_p)]
         L.pb200_comm_unique_id.argtypes = [C.c_char_p]
         L.pb200_attach_comm.argtypes = [C.c_void_p, C.c_char_p]
@@ -154,6 +155,16 @@ def launch_plan(nx, ny, resident_ctas=592):
     """(nbA, nxA, nbB, ctas, windows, warps_per_cta): how the iteration kernels cut an nx x ny block into bands."""
     v = (C.c_int32 * 6)()
     _check(lib().pb200_launch_plan(nx, ny, resident_ctas, v))
+    return tuple(v)
+
+
+def tile_plan(nx, ny, sms=148, smem_bytes=231000):
+    """(R, C, tr, tc): tiles of the resident loop kernel for an nx x ny block, or None if the block does not fit."""
+    v = (C.c_int32 * 4)()
+    st = lib().pb200_tile_plan(nx, ny, sms, smem_bytes, v)
+    if st == 5:
+        return None
+    _check(st)
     return tuple(v)
 
 

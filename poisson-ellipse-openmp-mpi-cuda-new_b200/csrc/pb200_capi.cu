@@ -271,6 +271,23 @@ pb200_status pb200_launch_plan(int32_t nx, int32_t ny, int32_t resident_ctas, in
     return PB200_OK;
 }
 
+pb200_status pb200_tile_plan(int32_t nx, int32_t ny, int32_t sms, int64_t smem_bytes, int32_t plan[4]) {
+    if (nx < 1 || ny < 1 || sms < 1 || smem_bytes < 1 || !plan) {
+        set_error("bad arguments");
+        return PB200_ERR_INVALID;
+    }
+    int R = 0, C = 0, tr = 0, tc = 0;
+    if (!tile_plan(nx, ny, std::min<int>(sms, TL_MAX_BLOCKS), static_cast<size_t>(smem_bytes), R, C, tr, tc)) {
+        set_error("a block of %d x %d cells does not fit the shared memory of %d SMs", nx, ny, sms);
+        return PB200_ERR_TOO_LARGE;
+    }
+    plan[0] = R;
+    plan[1] = C;
+    plan[2] = tr;
+    plan[3] = tc;
+    return PB200_OK;
+}
+
 pb200_status pb200_decompose_2d(int32_t M, int32_t N, int32_t Px, int32_t Py, int32_t rank, int32_t *i_start,
                                 int32_t *i_end, int32_t *j_start, int32_t *j_end) {
     if (M < 2 || N < 2 || Px < 1 || Py < 1 || rank < 0 || rank >= Px * Py || !i_start || !i_end || !j_start || !j_end) {

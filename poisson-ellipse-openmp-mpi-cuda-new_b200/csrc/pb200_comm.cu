@@ -272,6 +272,7 @@ pb200_status Solver::peer_attach(const uint8_t *blobs, int nranks) {
     }
     peer_ready = true;
     c.multi = 2;
+    plan_launch(); // blocks that fit in shared memory now run the resident loop kernel across the GPUs
     if (graph_exec) { cudaGraphExecDestroy(graph_exec); graph_exec = nullptr; }
     return PB200_OK;
 }
@@ -280,7 +281,10 @@ void Solver::peer_release() {
     for (void *p : ipc_opened) cudaIpcCloseMemHandle(p);
     ipc_opened.clear();
     peer_ready = false;
-    if (c.multi == 2) c.multi = 1;
+    if (c.multi == 2) {
+        c.multi = 1;
+        use_tile = false;
+    }
 }
 
 pb200_status Solver::reduce_norms_host(double *) {

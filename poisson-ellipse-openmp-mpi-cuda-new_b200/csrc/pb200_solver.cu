@@ -190,6 +190,7 @@ Solver::~Solver() {
     if (part2) cudaFree(part2);
     if (trace) cudaFree(trace);
     if (norms) cudaFree(norms);
+    if (tile_slots) cudaFree(tile_slots);
     if (h_ctl) cudaFreeHost(h_ctl);
     f.release();
     if (stream) cudaStreamDestroy(stream);
@@ -252,6 +253,79 @@ MarchPlan march_plan(int resident_blocks, int wn, int nx) {
     return m;
 }
 
+// Tiles of tile_loop_kernel: tr x tc tiles of at most R x C cells, one per CTA, at most one CTA per SM. Small blocks use
+// fewer CTAs (a barrier among few is cheaper than idle threads are useful): about one cell per thread at least.
+bool tile_plan(int nx, int ny, int sms, size_t smem_max, int &R, int &C, int &tr, int &tc) {
+    const long long cells = static_cast<long long>(nx) * ny;
+    int want = static_cast<int>(std::min<long long>(sms, (cells + TL_THREADS - 1) / TL_THREADS));
+    want = std::max(1, std::min(want, TL_MAX_BLOCKS));
+    double best = 1e300;
+    bool found = false;
+    for (int c_try = 1; c_try <= want; ++c_try) {
+        const int r_try = std::min(want / c_try, nx);
+        if (r_try < 1 || c_try > ny) continue;
+        const int Rq = (nx + r_try - 1) / r_try, Cq = (ny + c_try - 1) / c_try;
+        if (Cq > TL_MAXC || 2 * (Rq + Cq) > TL_NH * TL_THREADS) continue;
+        if (tile_smem_bytes(Rq, Cq) > smem_max) continue;
+        // cost: the largest tile's cells plus its halo ring (recomputed p'; column halos are strided global reads)
+        const double cost = static_cast<double>(Rq) * Cq + 2.0 * Cq + 6.0 * Rq;
+        if (cost < best) {
+            best = cost;
+            R = Rq;
+            C = Cq;
+            tr = (nx + Rq - 1) / Rq;
+            tc = (ny + Cq - 1) / Cq;
+            found = true;
+        }
+    }
+    return found;
+}
+
+void Solver::plan_tile(int sms) {
+    use_tile = false;
+    const char *env = std::getenv("PB200_TILE"), *env_loop = std::getenv("PB200_LOOP");
+    if ((env && atoi(env) == 0) || (env_loop && atoi(env_loop) == 0)) return; // tuning / tests: the other kernels
+    if (c.multi == 1) return; // NCCL mode exchanges between kernels: the marching kernels
+    int coop = 0, smem_optin = 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    cudaFuncAttributes fa{};
+    if (!coop || cudaFuncGetAttributes(&fa, tile_loop_kernel) != cudaSuccess) {
+        cudaGetLastError();
+        return;
+    }
+    const size_t smem_max = static_cast<size_t>(smem_optin) - fa.sharedSizeBytes;
+    // Every rank must take the same decision (a rank in this kernel and its neighbour in the marching kernels would wait
+    // for each other for ever): it is taken on the LARGEST block of the decomposition, which is the same number everywhere.
+    const int nx_max = (prm.M - 1 + Px - 1) / Px, ny_max = (prm.N - 1 + Py - 1) / Py;
+    int R = 0, C = 0, tr = 0, tc = 0;
+    if (!tile_plan(nx_max, ny_max, std::min(sms, TL_MAX_BLOCKS), smem_max, R, C, tr, tc)) return;
+    int R2 = 0, C2 = 0, tr2 = 0, tc2 = 0; // this rank's own block: its own best cut, else the largest block's tile size
+    if (tile_plan(f.g.nx, f.g.ny, std::min(sms, TL_MAX_BLOCKS), smem_max, R2, C2, tr2, tc2)) {
+        R = R2;
+        C = C2;
+    }
+    tr = (f.g.nx + R - 1) / R;
+    tc = (f.g.ny + C - 1) / C;
+    const size_t smem = tile_smem_bytes(R, C);
+    if (cudaFuncSetAttribute(tile_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_max)) != cudaSuccess) {
+        cudaGetLastError();
+        return;
+    }
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, tile_loop_kernel, TL_THREADS, smem) != cudaSuccess || occ < 1) {
+        cudaGetLastError();
+        return;
+    }
+    if (static_cast<long long>(tr) * tc > static_cast<long long>(occ) * sms) return;
+    use_tile = true;
+    tile_R = R;
+    tile_C = C;
+    tile_tr = tr;
+    tile_tc = tc;
+    tile_smem = smem;
+}
+
 void Solver::plan_launch() {
     wn = (f.g.ny + K1_OWN - 1) / K1_OWN;
     int sms = 148, occ1 = 1, occ2 = 1;
@@ -297,6 +371,7 @@ void Solver::plan_launch() {
             }
         }
     }
+    plan_tile(sms);
     norms_grid = dim3((f.g.ny + 255) / 256, std::min(f.g.nx, 512), 1);
     init_grid = dim3((f.g.ny + INIT_THREADS - 1) / INIT_THREADS, std::min(f.g.nx, 1024), 1);
 }
@@ -344,6 +419,11 @@ pb200_status Solver::create(const pb200_params &params) {
     const size_t nb3 = std::max(static_cast<size_t>(norms_grid.x) * norms_grid.y, static_cast<size_t>(init_grid.x) * init_grid.y);
     CK(cudaMalloc(&part2, std::max(2 * nb2, 3 * nb3) * sizeof(double))); // norms_kernel: 3 partials per block
     CK(cudaMalloc(&norms, 8 * sizeof(double)));
+    CK(cudaMalloc(&tile_slots, TL_SLOT_WORDS * sizeof(unsigned long long)));
+    if (!mail) { // the mailbox of the in-kernel all-reduce (peer_export hands it to the other ranks)
+        CK(cudaMalloc(&mail, MAIL_DOUBLES * sizeof(double)));
+        CK(cudaMemset(mail, 0, MAIL_DOUBLES * sizeof(double)));
+    }
     if (c.trace_len > 0) {
         CK(cudaMalloc(&trace, static_cast<size_t>(c.trace_len) * 3 * sizeof(double)));
         CK(cudaMemsetAsync(trace, 0, static_cast<size_t>(c.trace_len) * 3 * sizeof(double), stream));
@@ -465,7 +545,7 @@ pb200_status Solver::solve(pb200_result *res) {
     CK(cudaMemsetAsync(norms, 0, 8 * sizeof(double), stream));
     // peer-memory mode: clear the mailbox; the NCCL all-reduce of the start-up (z,r) below doubles as the barrier that
     // keeps any rank from posting into a mailbox that has not been cleared yet
-    if (c.multi == 2) CK(cudaMemsetAsync(mail, 0, MAIL_DOUBLES * sizeof(double), stream));
+    if (c.multi == 2 || use_tile) CK(cudaMemsetAsync(mail, 0, MAIL_DOUBLES * sizeof(double), stream));
     launch_init();
     ++launches;
     if (c.multi) {
@@ -492,7 +572,39 @@ pb200_status Solver::solve(pb200_result *res) {
     const bool use_graph = prm.use_graph != 0 && c.multi != 1;
     CK(cudaEventRecord(ev_start, stream));
     long long k = 1;
-    if (use_loop) { // one cooperative launch runs every iteration; delta and max_iter are enforced on the device
+    if (use_tile) { // one cooperative launch per rank runs every iteration, halo and sums included (pb200_tile.cuh)
+        CK(cudaMemsetAsync(tile_slots, 0, TL_SLOT_WORDS * sizeof(unsigned long long), stream));
+        TileArgs ta{};
+        ta.w = f.w;
+        ta.r = f.r;
+        ta.p[0] = f.p[0];
+        ta.p[1] = f.p[1];
+        ta.a = f.a;
+        ta.b = f.b;
+        ta.D = f.D;
+        ta.cls = f.cls;
+        ta.slots = tile_slots;
+        ta.trace = trace;
+        ta.ctl = ctl;
+        ta.g = f.g;
+        ta.c = c;
+        ta.R = tile_R;
+        ta.C = tile_C;
+        ta.tc = tile_tc;
+        ta.safe = safe_div ? 1 : 0;
+        ta.pv = pv;
+        if (c.multi == 0) { // one GPU: the all-reduce still goes through the (own) mailbox
+            ta.pv = PeerView{};
+            ta.pv.nranks = 1;
+            ta.pv.rank = 0;
+            ta.pv.mail[0] = mail;
+        }
+        void *args[] = {&ta};
+        CK(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(tile_loop_kernel), dim3(tile_tr * tile_tc, 1, 1),
+                                       dim3(TL_THREADS, 1, 1), args, tile_smem, stream));
+        ++launches;
+        k = c.max_iter + 1;
+    } else if (use_loop) { // one cooperative launch runs every iteration; delta and max_iter are enforced on the device
         CellLoopArgs la{};
         la.w = f.w;
         la.r = f.r;
@@ -520,7 +632,7 @@ pb200_status Solver::solve(pb200_result *res) {
         ++k;
     }
     CK(cudaGetLastError());
-    if (!use_loop && use_graph && !graph_exec && c.max_iter > 1) {
+    if (!use_loop && !use_tile && use_graph && !graph_exec && c.max_iter > 1) {
         cudaGraph_t graph = nullptr;
         CK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
         launch_iteration(2, false);

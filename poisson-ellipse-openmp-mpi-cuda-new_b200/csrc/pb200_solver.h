@@ -2,6 +2,7 @@
 #pragma once
 #include "../../include/poisson_b200.h"
 #include "pb200_kernels.cuh"
+#include "pb200_tile.cuh"
 
 #include <vector>
 
@@ -32,6 +33,9 @@ struct MarchPlan {
     Bands bands; // how the rows are cut
 };
 MarchPlan march_plan(int resident_blocks, int wn, int nx);
+// tile_loop_kernel's cut of an nx x ny block for `sms` CTAs with `smem_max` bytes of dynamic shared memory each:
+// false if the block does not fit. R x C = tile size, tr x tc = tiles.
+bool tile_plan(int nx, int ny, int sms, size_t smem_max, int &R, int &C, int &tr, int &tc);
 // single-GPU blocks of at most this many cells that do not fit cell_loop_kernel run cell_loop_stream_kernel (measured
 // cross-over with the marching kernels)
 constexpr double LOOP_STREAM_MAX_POINTS = 1.3e6;
@@ -71,6 +75,11 @@ struct Solver {
     bool use_loop = false; // small block: the whole loop is one cooperative launch (cell_loop_kernel)
     dim3 loop_grid;
     int loop_cells = 1; // cells per thread of cell_loop_kernel; 0: cell_loop_stream_kernel
+    // blocks that fit in shared memory: the whole loop in one cooperative launch of tile_loop_kernel, one or several GPUs
+    bool use_tile = false;
+    int tile_R = 0, tile_C = 0, tile_tr = 0, tile_tc = 0;
+    size_t tile_smem = 0;
+    unsigned long long *tile_slots = nullptr; // the CTAs' partial sums as tagged words
     long long launches = 0;
     long long last_iter = 0;
     double t_setup = 0.0;
@@ -87,6 +96,7 @@ struct Solver {
     pb200_status create(const pb200_params &params);
     pb200_status run_setup();
     void plan_launch();
+    void plan_tile(int sms);
     void launch_iteration(long long k, bool first);
     void launch_k1(const K1Args &a, bool first);
     void launch_k2(const K2Args &a);

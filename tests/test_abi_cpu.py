@@ -72,6 +72,27 @@ def test_launch_plan_covers_every_row_exactly_once():
                 assert nx - nxA <= nx // 5 and (nx - nxA) / nbB <= nxA / nbA + 1, (nx, ny, plan)
 
 
+def test_tile_plan_covers_the_block_and_fits():
+    """The resident loop kernel's tiles: at most one per SM, every cell in exactly one tile, tile + halo within the
+    shared memory given, halo ring within two cells per thread; blocks beyond ~1.3 M cells are refused."""
+    import random
+    rnd = random.Random(11)
+    cases = [(39, 39), (1, 1), (1, 5000), (5000, 1), (399, 599), (799, 1199), (1200, 800), (1199, 799), (2399, 1600),
+             (1000, 1300), (3, 100000), (148, 148), (149, 1024), (1100, 1180)]
+    cases += [(rnd.randint(1, 1500), rnd.randint(1, 1500)) for _ in range(300)]
+    for sms, smem in ((148, 231000), (132, 231000), (148, 100000), (7, 231000)):
+        for nx, ny in cases:
+            plan = pb.tile_plan(nx, ny, sms, smem)
+            if plan is None:
+                assert nx * ny * 24 > sms * smem * 0.80, (nx, ny, sms, smem)          # only blocks that really do not fit
+                continue
+            R, C, tr, tc = plan
+            assert 1 <= tr * tc <= sms and (tr - 1) * R < nx <= tr * R and (tc - 1) * C < ny <= tc * C, (nx, ny, plan)
+            assert ((R + 2) * (C + 2) + 2 * R * C) * 8 + (R + 2) * (C + 2) + R * C <= smem and 2 * (R + C) <= 2048 and C <= 1024, (nx, ny, plan)
+    assert pb.tile_plan(1200, 800) is not None and pb.tile_plan(399, 599) is not None          # 2400x3200 on 8 GPUs; configs[1]
+    assert pb.tile_plan(2399, 3199) is None and pb.tile_plan(8191, 8191) is None
+
+
 def test_bad_arguments_are_rejected():
     with pytest.raises(pb.PB200Error):
         pb.decompose_2d(40, 40, 2, 2, 4)

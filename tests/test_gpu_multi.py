@@ -74,20 +74,30 @@ def test_results_do_not_depend_on_gpu_count(tmp_path, golden, M, N, gpus, extra)
 
 
 @pytest.mark.parametrize("M,N,gpus,extra", [(400, 600, 2, ()), (400, 600, 2, ("--grid", "2x1")), (37, 53, 2, ()),
-                                            (400, 600, 4, ()), (400, 600, 8, ())])
-def test_peer_memory_and_nccl_modes_agree_bitwise(tmp_path, M, N, gpus, extra):
-    """The default multi-GPU mode moves halos and partial sums through peer memory inside the kernels; --comm nccl
-    uses NCCL calls between the kernels. Same arithmetic, same rank-ordered sums: identical results."""
+                                            (400, 600, 4, ()), (400, 600, 8, ()), (1016, 2030, 2, ())])
+def test_peer_memory_and_nccl_modes_agree(tmp_path, monkeypatch, M, N, gpus, extra):
+    """The default multi-GPU mode moves halos and partial sums through peer memory inside the kernels; --comm nccl uses
+    NCCL calls between the kernels. With the two marching kernels in both (PB200_LOOP=0) it is the same arithmetic and the
+    same rank-ordered sums: identical results. Blocks that fit in shared memory run the resident loop kernel in peer mode
+    (one launch per GPU for the whole solve): other partial sums, so the bar between GPU counts applies."""
     need(gpus)
-    _, a, wa = run_cli(tmp_path, M, N, gpus, extra + ("--comm", "peer"))
     _, b, wb = run_cli(tmp_path, M, N, gpus, extra + ("--comm", "nccl"))
-    assert a["iterations"] == b["iterations"]
+    monkeypatch.setenv("PB200_LOOP", "0")
+    _, a, wa = run_cli(tmp_path, M, N, gpus, extra + ("--comm", "peer"))
+    assert a["iterations"] == b["iterations"] and a["kernel_launches"] > 2 * a["iterations"]
     assert abs(a["w_norm_E"] - b["w_norm_E"]) <= 1e-12 * abs(b["w_norm_E"])
     np.testing.assert_allclose(wa, wb, rtol=0, atol=1e-12)
+    monkeypatch.delenv("PB200_LOOP")
+    _, t, wt = run_cli(tmp_path, M, N, gpus, extra + ("--comm", "peer"))
+    assert t["iterations"] == b["iterations"] and t["kernel_launches"] <= 6          # reset, init, its scalar tail, the loop, norms
+    for f in ("w_norm_E", "w_max", "diff_norm", "zr", "err_max_in_D"):
+        assert abs(t[f] - b[f]) <= 1e-10 * abs(b[f]), f
+    np.testing.assert_allclose(wt, wb, rtol=0, atol=1e-11)
 
 
-def test_multi_gpu_fixed_iterations_and_no_graph(tmp_path):
+def test_multi_gpu_fixed_iterations_and_no_graph(tmp_path, monkeypatch):
     need(2)
+    monkeypatch.setenv("PB200_LOOP", "0")          # the marching kernels: the graph only exists there
     _, a, wa = run_cli(tmp_path, 300, 200, 2, ("--fixed-iters", "37"))
     _, b, wb = run_cli(tmp_path, 300, 200, 2, ("--fixed-iters", "37", "--no-graph"))
     assert a["iterations"] == b["iterations"] == 37

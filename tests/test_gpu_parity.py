@@ -329,43 +329,74 @@ def test_solve_800x1200(oracle, golden):
                                     (100, 140, {"fixed_iters": 75}), (64, 64, {"max_iter": 9}), (65, 300, {"eps": 1e-3}),
                                     (500, 640, {}), (2, 2, {}), (3, 130, {}), (800, 1200, {}), (700, 900, {"fixed_iters": 40})])
 def test_resident_loop_and_two_kernel_paths_agree(monkeypatch, m, n, kw):
-    """Small single-GPU blocks run the whole loop as one cooperative launch with a resident thread per cell
-    (cell_loop_kernel: 1, 2 or 4 cells per thread; above 454 K cells cell_loop_stream_kernel); PB200_LOOP=0 forces the two marching kernels. Element-wise arithmetic
-    is the same term by term, the grouping of the partial sums is not: iteration counts are equal, the per-iteration
-    scalars agree to 1e-10, the solution to 1e-12 (the same bar as between GPU counts)."""
+    """Blocks that fit in shared memory run the whole loop as ONE cooperative launch (tile_loop_kernel: a tile per SM,
+    state in shared memory); PB200_TILE=0 selects the older resident kernels (cell_loop_kernel: 1, 2 or 4 cells per thread
+    in registers; above 454 K cells cell_loop_stream_kernel), PB200_LOOP=0 the two marching kernels. Element-wise
+    arithmetic is the same term by term, the grouping of the partial sums is not: iteration counts are equal, the
+    per-iteration scalars agree to 1e-10, the solution to 1e-12 (the same bar as between GPU counts)."""
     if "norm_mode" in kw:
         kw = dict(kw, norm_mode=pb.NORM_STAGE0)
     outs = []
-    for mode in ("0", "1"):
-        monkeypatch.setenv("PB200_LOOP", mode)
+    for loop, tile in (("0", "1"), ("1", "0"), ("1", "1")):
+        monkeypatch.setenv("PB200_LOOP", loop)
+        monkeypatch.setenv("PB200_TILE", tile)
         with pb.Solver(pb.default_params(m, n, trace_len=8, **kw)) as s:
             res = s.solve()
             res2 = s.solve()          # and again on the same handle
             assert res2.iterations == res.iterations and res2.zr == res.zr
             outs.append((res, s.solution(), s.trace(8), res.kernel_launches))
-    (r0, w0, t0, l0), (r1, w1, t1, l1) = outs
-    assert l1 <= 4 and (l0 > l1 or r0.iterations < 2)          # the loop path is one launch (+ reset, init, norms)
-    assert r0.iterations == r1.iterations and r0.stop_reason == r1.stop_reason
-    assert r0.first_converged_iter == r1.first_converged_iter
-    assert rel(r0.diff_norm, r1.diff_norm) < 1e-9 and rel(r0.w_norm_E, r1.w_norm_E) < RTOL_NORM and rel(r0.zr, r1.zr) < 1e-9
-    assert rel(r0.alpha, r1.alpha) < 1e-9 and rel(r0.beta, r1.beta) < 1e-9
+    (r0, w0, t0, l0) = outs[0]
+    for (r1, w1, t1, l1) in outs[1:]:
+        assert l1 <= 4 and (l0 > l1 or r0.iterations < 2)          # the loop paths are one launch (+ reset, init, norms)
+        assert r0.iterations == r1.iterations and r0.stop_reason == r1.stop_reason
+        assert r0.first_converged_iter == r1.first_converged_iter
+        assert rel(r0.diff_norm, r1.diff_norm) < 1e-9 and rel(r0.w_norm_E, r1.w_norm_E) < RTOL_NORM and rel(r0.zr, r1.zr) < 1e-9
+        assert rel(r0.alpha, r1.alpha) < 1e-9 and rel(r0.beta, r1.beta) < 1e-9
+        np.testing.assert_allclose(t0, t1, rtol=1e-10, atol=0)
+        np.testing.assert_allclose(w0, w1, rtol=0, atol=1e-12)
+
+
+@pytest.mark.parametrize("m,n,kw", [(2, 2, {}), (2, 300, {}), (300, 2, {}), (33, 1500, {}), (1500, 33, {}), (149, 1025, {}),
+                                    (1000, 1300, {"fixed_iters": 60}), (1100, 1180, {"fixed_iters": 25}),
+                                    (257, 130, {"eps": 1e-95, "fixed_iters": 12}), (130, 260, {"eps": 1e-3, "ell_ax": 0.7, "rhs_mode": 1})])
+def test_tile_loop_kernel_shapes(monkeypatch, oracle, m, n, kw):
+    """tile_loop_kernel on shapes that stress its tiling (single rows and columns of tiles, ragged last tiles, the largest
+    blocks that fit, coefficients outside the fast-division window) against the two marching kernels and, where the
+    oracle is quick, against the oracle."""
+    outs = []
+    for loop in ("1", "0"):
+        monkeypatch.setenv("PB200_LOOP", loop)
+        monkeypatch.delenv("PB200_TILE", raising=False)
+        with pb.Solver(pb.default_params(m, n, trace_len=8, **kw)) as s:
+            res = s.solve()
+            outs.append((res, s.solution(), s.trace(8)))
+    (r1, w1, t1), (r0, w0, t0) = outs
+    assert r1.kernel_launches <= 4 < r0.kernel_launches or r0.iterations < 2
+    assert r0.iterations == r1.iterations and r0.stop_reason == r1.stop_reason and r0.safe_mode == r1.safe_mode
+    assert rel(r0.w_norm_E, r1.w_norm_E) < RTOL_NORM and rel(r0.diff_norm, r1.diff_norm) < 1e-9
     np.testing.assert_allclose(t0, t1, rtol=1e-10, atol=0)
     np.testing.assert_allclose(w0, w1, rtol=0, atol=1e-12)
+    if m * n <= 200000 and "eps" not in kw:
+        ores, ow, _ = oracle.solve(m, n, want_w=True)
+        assert r1.iterations == ores.iterations and rel(r1.w_norm_E, ores.w_norm_E) < RTOL_NORM
+        np.testing.assert_allclose(w1, ow, rtol=0, atol=1e-11)
 
 
 def test_resident_loop_first_iteration_bitwise(monkeypatch):
-    """After ONE iteration p' (stored by the K1 phase) depends on no summed scalar: bit-identical between the two paths;
-    w and r agree to the last bits of alpha."""
+    """After ONE iteration p' (stored by the K1 phase) depends on no summed scalar: bit-identical between the marching
+    kernels, the register-resident loop kernel and the shared-memory-resident one; w and r agree to the last bits of alpha."""
     outs = []
-    for mode in ("0", "1"):
-        monkeypatch.setenv("PB200_LOOP", mode)
+    for loop, tile in (("0", "1"), ("1", "0"), ("1", "1")):
+        monkeypatch.setenv("PB200_LOOP", loop)
+        monkeypatch.setenv("PB200_TILE", tile)
         with pb.Solver(pb.default_params(130, 260, max_iter=1)) as s:
             res = s.solve()
             assert res.iterations == 1
             ptr, pitch, nx, ny = s.field_ptr(2)          # p of the last iteration
             outs.append((fetch_field(ptr, pitch, nx, ny), s.solution()))
-    assert np.array_equal(outs[0][0], outs[1][0])
-    np.testing.assert_allclose(outs[0][1], outs[1][1], rtol=1e-14, atol=0)
+    for o in outs[1:]:
+        assert np.array_equal(outs[0][0], o[0])
+        np.testing.assert_allclose(outs[0][1], o[1], rtol=1e-14, atol=0)
 
 
 def test_graph_and_plain_launches_agree_bitwise(monkeypatch):
