@@ -14,8 +14,9 @@
 //            global memory and, on a block edge with a neighbour GPU, straight into that GPU's ring    -> all-reduce 2
 //   the scalar tail of the iteration (S4:893-906, 926-932) in every thread, identically.
 //
-// A thread owns a column of the tile and marches down its rows: p' of the rows above and below and the flux through the
-// upper face stay in registers; the columns left and right come from shared memory.
+// A thread owns a pair of adjacent columns of the tile and marches down its rows: p' of the current row and the fluxes
+// through its upper faces stay in registers (each face flux is computed once), the columns left and right of the pair
+// come from shared memory.
 //
 // An all-reduce is the grid barrier, built from "tagged words": a double travels as two 64-bit words, each carrying half
 // of its bits and the number of the reduction, so a reader that sees the tag has the payload -- no flag, no fence and no
@@ -33,10 +34,10 @@
 
 namespace pb200 {
 
-constexpr int TL_THREADS = 1024;
-constexpr int TL_NH = 2;           // halo cells per thread at most: 2 (R + C) <= TL_NH * TL_THREADS
+constexpr int TL_THREADS = 512;    // one CTA per SM, up to 128 registers per thread
+constexpr int TL_NH = 4;           // halo cells per thread at most: 2 (R + C) <= TL_NH * TL_THREADS
 constexpr int TL_MAX_BLOCKS = 192; // one CTA per SM
-constexpr int TL_MAXC = 1024;      // a tile is at most this wide: one thread per column
+constexpr int TL_MAXC = 1024;      // a tile is at most this wide: one thread per pair of columns
 constexpr int TL_SLOT_WORDS = 4 * TL_MAX_BLOCKS; // CTA partials: [value k < 2][half][CTA]
 constexpr int TL_MAIL_WORDS = 64;  // per GPU: [parity][rank < 8][value k < 2][half]  (= MAIL_DOUBLES: the same 512 bytes)
 static_assert(TL_MAIL_WORDS == MAIL_DOUBLES, "the resident loop kernel uses the marching kernels' mailbox");
@@ -55,8 +56,15 @@ struct TileArgs {
     PeerView pv;                // mail[q]: every rank's mailbox (one GPU: nranks = 1, its own); r_*: c.multi == 2
 };
 
+// Shared-memory layout of a tile of R x C cells (all pitches even, so that a thread's pair of columns is one 16-byte access):
+//   sP   (R+2) rows of PC = C+4 (rounded up to even) doubles: p' with its halo; own cell (lr, lc) at [(lr+1)*PC + lc + 2],
+//        the left halo column at index 1, the right one at Ct + 2
+//   sR, sAp   R rows of Cp = C rounded up to even doubles: r and A p' of the own cells, [lr*Cp + lc]
+//   sD   bytes indexed like sP: diagonal class;   sK   bytes indexed like sR: the coefficient classes of the cell's stencil
+__host__ __device__ inline int tile_pc(int C) { return (C + 4 + 1) & ~1; }
+__host__ __device__ inline int tile_cp(int C) { return (C + 1) & ~1; }
 __host__ __device__ inline size_t tile_smem_bytes(int R, int C) {
-    const size_t halo = (size_t)(R + 2) * (size_t)(C + 2), own = (size_t)R * (size_t)C;
+    const size_t halo = (size_t)(R + 2) * (size_t)tile_pc(C), own = (size_t)R * (size_t)tile_cp(C);
     return (halo + 2 * own) * sizeof(double) + ((halo + 15) / 16) * 16 + ((own + 15) / 16) * 16;
 }
 
@@ -104,7 +112,7 @@ __device__ __forceinline__ unsigned tl_poll(const unsigned long long *p, unsigne
 // 148 CTAs -- 148 x 148 sector reads per polling round on the same few cache lines.)
 template <int NV>
 __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &A, const unsigned gen, const unsigned wmask,
-                                               const bool publish, double (*s_red)[32], unsigned (*s_words)[TL_MAX_BLOCKS],
+                                               const bool publish, double (*s_red)[TL_THREADS / 32], unsigned (*s_words)[TL_MAX_BLOCKS],
                                                double *s_bc, int *s_fail) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nblocks = gridDim.x, bid = blockIdx.x;
@@ -184,10 +192,17 @@ __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &
     return *reinterpret_cast<volatile int *>(s_fail) == 0;
 }
 
+// a thread's pair of adjacent doubles in shared memory (16-byte aligned by construction of the layout)
+__device__ __forceinline__ double2 lds2(const double *p) { return *reinterpret_cast<const double2 *>(p); }
+__device__ __forceinline__ void sts2(double *p, double a, double b, bool both) {
+    if (both) *reinterpret_cast<double2 *>(p) = make_double2(a, b);
+    else *p = a;
+}
+
 __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs A) {
     extern __shared__ __align__(16) unsigned char tl_smem[];
     __shared__ double2 s_lut[16];
-    __shared__ double s_red[2][32];
+    __shared__ double s_red[2][TL_THREADS / 32];
     __shared__ unsigned s_words[4][TL_MAX_BLOCKS];
     __shared__ double s_bc[2];
     __shared__ int s_fail;
@@ -199,54 +214,63 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
     const int i_lo = 1 + ti * A.R, i_hi = min(g.nx, i_lo + A.R - 1);
     const int j_lo = 1 + tj * A.C, j_hi = min(g.ny, j_lo + A.C - 1);
     const int Rt = i_hi - i_lo + 1, Ct = j_hi - j_lo + 1;
-    const int PC = A.C + 2; // pitch of the haloed arrays
-    const size_t n_halo = (size_t)(A.R + 2) * PC, n_own = (size_t)A.R * A.C;
-    double *sP = reinterpret_cast<double *>(tl_smem); // p', (R+2) x (C+2): own cell (lr, lc) at [(lr+1) * PC + lc + 1]
-    double *sR = sP + n_halo;                         // r of the own cells, [lr * Ct + lc]
-    double *sAp = sR + n_own;                         // A p' of the own cells
-    unsigned char *sD = reinterpret_cast<unsigned char *>(sAp + n_own); // diagonal class, indexed like sP
-    unsigned char *sK = sD + ((n_halo + 15) / 16) * 16; // coefficient classes of a cell's stencil: a(c) | a(up) << 2 | b(c) << 4 | b(right) << 6
+    const int PC = tile_pc(A.C), Cp = tile_cp(A.C);
+    const size_t n_halo = (size_t)(A.R + 2) * PC, n_own = (size_t)A.R * Cp;
+    double *sP = reinterpret_cast<double *>(tl_smem);
+    double *sR = sP + n_halo;
+    double *sAp = sR + n_own;
+    unsigned char *sD = reinterpret_cast<unsigned char *>(sAp + n_own);
+    unsigned char *sK = sD + ((n_halo + 15) / 16) * 16; // a(c) | a(up) << 2 | b(c) << 4 | b(right) << 6
     const int P = g.pitch;
-    const size_t o00 = (size_t)(i_lo - 1) * P + (size_t)(j_lo - 1); // global offset of tile-local (0, 0)
+    const size_t o00 = (size_t)(i_lo - 1) * P + (size_t)(j_lo - 1); // global offset of the tile's halo corner (row i_lo-1, column j_lo-1)
     const bool safe = A.safe != 0;
     const bool pw1 = (c.pow2 & 1) != 0, pw2 = (c.pow2 & 2) != 0;
     const double h1 = c.h1, h2 = c.h2, rh1 = c.rh1, rh2 = c.rh2, mih1 = c.mih1, mih2 = c.mih2, inv_eps = c.inv_eps;
 
     if (tid < 16) s_lut[tid] = make_double2(c.lutD[tid], c.lutR[tid]);
     if (tid == 0) s_fail = 0;
-    for (int q = tid; q < (Rt + 2) * (Ct + 2); q += TL_THREADS) {
+    for (int q = tid; q < (int)n_halo; q += TL_THREADS) { // p starts from zero (S4:805-834); pads hold zeros for ever
+        sP[q] = 0.0;
+        sD[q] = (unsigned char)DCLS_RING;
+    }
+    for (int q = tid; q < (int)n_own; q += TL_THREADS) {
+        sR[q] = 0.0;
+        sAp[q] = 0.0;
+        sK[q] = 0;
+    }
+    __syncthreads();
+    for (int q = tid; q < (Rt + 2) * (Ct + 2); q += TL_THREADS) { // halo coordinates (hr, hc): row i_lo-1+hr, column j_lo-1+hc
         const int hr = q / (Ct + 2), hc = q - hr * (Ct + 2);
-        sP[hr * PC + hc] = 0.0; // S4:805-834: p starts from z, the ring from zero
-        sD[hr * PC + hc] = (unsigned char)(tl_class(A.cls, g.cpitch, i_lo - 1 + hr, j_lo - 1 + hc) >> 4);
+        sD[hr * PC + hc + 1] = (unsigned char)(tl_class(A.cls, g.cpitch, i_lo - 1 + hr, j_lo - 1 + hc) >> 4);
     }
     for (int q = tid; q < Rt * Ct; q += TL_THREADS) {
         const int lr = q / Ct, lc = q - lr * Ct, li = i_lo + lr, lj = j_lo + lc;
         const unsigned kc = tl_class(A.cls, g.cpitch, li, lj), ku = tl_class(A.cls, g.cpitch, li + 1, lj),
                        kr = tl_class(A.cls, g.cpitch, li, lj + 1);
-        sK[q] = (unsigned char)((kc & 3u) | ((ku & 3u) << 2) | (((kc >> 2) & 3u) << 4) | (((kr >> 2) & 3u) << 6));
-        sR[q] = A.r[(size_t)li * P + lj]; // S4:813: r = B (setup / reset kernel)
+        sK[lr * Cp + lc] = (unsigned char)((kc & 3u) | ((ku & 3u) << 2) | (((kc >> 2) & 3u) << 4) | (((kr >> 2) & 3u) << 6));
+        sR[lr * Cp + lc] = A.r[(size_t)li * P + lj]; // S4:813: r = B (setup / reset kernel)
     }
-    // Thread layout: one thread per column of the tile; when the tile is narrower than half the CTA, TY groups of
-    // threads share the rows. Lanes past the last column shadow it (same reads, no stores, nothing summed), so that
-    // every warp that works is whole and its votes are warp-wide.
-    const int TXp = ((Ct + 31) / 32) * 32, TY = max(1, min(TL_THREADS / TXp, Rt));
+    // Thread layout: a thread owns a PAIR of adjacent columns and marches down its rows; when the tile is narrow, TY groups
+    // of threads share the rows. Lanes past the last pair shadow it (same reads, no stores, nothing summed), so that every
+    // warp that works is whole and its votes are warp-wide. An odd last column is a pair whose second cell is not owned.
+    const int NPAIR = (Ct + 1) / 2, TXp = ((NPAIR + 31) / 32) * 32, TY = max(1, min(TL_THREADS / TXp, Rt));
     const int ty = tid / TXp, tx = tid - ty * TXp;
-    const bool work = ty < TY;                 // warp-uniform: TXp is a multiple of 32
-    const bool own = work && tx < Ct;
-    const int txc = min(tx, Ct - 1);
+    const bool work = ty < TY;                  // warp-uniform: TXp is a multiple of 32
+    const int c0 = 2 * min(tx, NPAIR - 1);      // first column of the pair (tile-local, even)
+    const bool own0 = work && tx < NPAIR, own1 = own0 && c0 + 1 < Ct;
     const int RS = (Rt + TY - 1) / TY, r0 = min(Rt, ty * RS), r1 = min(Rt, r0 + RS);
-    // the thread's halo cells (loop-invariant): h < Ct: row 0; < 2 Ct: row Rt+1; < 2 Ct + Rt: column 0; else column Ct+1
+    // the thread's halo cells (loop-invariant): h < Ct: row above; < 2 Ct: row below; < 2 Ct + Rt: left column; else right column
     const int nh = 2 * Ct + 2 * Rt;
     int h_sm[TL_NH], h_gl[TL_NH];
 #pragma unroll
     for (int n = 0; n < TL_NH; ++n) {
-        const int h = (TL_THREADS - 1 - tid) + n * TL_THREADS; // the threads without a column come first
+        const int h = (TL_THREADS - 1 - tid) + n * TL_THREADS; // the threads without columns come first
         int hr = 0, hc = 0;
         if (h < Ct) { hr = 0; hc = 1 + h; }
         else if (h < 2 * Ct) { hr = Rt + 1; hc = 1 + h - Ct; }
         else if (h < 2 * Ct + Rt) { hr = 1 + h - 2 * Ct; hc = 0; }
         else { hr = 1 + h - 2 * Ct - Rt; hc = Ct + 1; }
-        h_sm[n] = (h < nh) ? hr * PC + hc : -1;
+        h_sm[n] = (h < nh) ? hr * PC + hc + 1 : -1;
         h_gl[n] = hr * P + hc;
     }
     __syncthreads();
@@ -255,6 +279,8 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
     double alpha = 0.0, beta = 0.0, diff = 0.0, denom = 0.0;
     long long k = 0;
     int status = STOP_MAX_ITER, conv_iter = 0;
+    const int ip0 = (r0 + 1) * PC + c0 + 2, ic0 = r0 * Cp + c0;  // the pair's first cell in the haloed / compact arrays
+    const size_t og0 = o00 + (size_t)(r0 + 1) * P + c0 + 1;      // ... and in global memory
     for (;;) {
         ++k; // S4:847-848
         const bool first = k == 1;
@@ -264,18 +290,26 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
 #pragma unroll
         for (int n = 0; n < TL_NH; ++n) r_halo[n] = (h_sm[n] >= 0) ? __ldcg(&A.r[o00 + h_gl[n]]) : 0.0;
         if (work) {
-            int ip = (r0 + 1) * PC + txc + 1, ic = r0 * Ct + txc;
-            for (int r = r0; r < r1; ++r, ip += PC, ic += Ct) {
-                const double rv = sR[ic];
-                const unsigned kd = sD[ip];
-                const double2 DR = s_lut[kd];
-                double z;
-                if (__any_sync(0xffffffffu, safe || kd == DCLS_GENERAL || !in_div_range(rv)))
-                    z = precond_div(rv, kd == DCLS_GENERAL ? __ldg(A.D + o00 + (size_t)(r + 1) * P + txc + 1) : DR.x);
-                else
-                    z = div_const_nocheck(rv, DR.x, DR.y);
-                const double pn = first ? z : z + beta * sP[ip];
-                if (own) sP[ip] = pn;
+            int ip = ip0, ic = ic0;
+            size_t og = og0;
+            for (int r = r0; r < r1; ++r, ip += PC, ic += Cp, og += P) {
+                const double2 rv = lds2(sR + ic);
+                const unsigned kd2 = *reinterpret_cast<const unsigned short *>(sD + ip), kd0 = kd2 & 0xffu, kd1 = kd2 >> 8;
+                const double2 DR0 = s_lut[kd0], DR1 = s_lut[kd1];
+                double z0, z1;
+                if (__any_sync(0xffffffffu, safe || kd0 == DCLS_GENERAL || kd1 == DCLS_GENERAL || !in_div_range(rv.x) || !in_div_range(rv.y))) {
+                    z0 = precond_div(rv.x, kd0 == DCLS_GENERAL ? __ldg(A.D + og) : DR0.x);
+                    z1 = precond_div(rv.y, kd1 == DCLS_GENERAL ? __ldg(A.D + og + 1) : DR1.x);
+                } else {
+                    z0 = div_const_nocheck(rv.x, DR0.x, DR0.y);
+                    z1 = div_const_nocheck(rv.y, DR1.x, DR1.y);
+                }
+                if (!first) {
+                    const double2 po = lds2(sP + ip);
+                    z0 = z0 + beta * po.x;
+                    z1 = z1 + beta * po.y;
+                }
+                if (own0) sts2(sP + ip, z0, z1, own1);
             }
         }
 #pragma unroll
@@ -291,59 +325,77 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
                 sP[ip] = first ? z : z + beta * sP[ip];
             }
         __syncthreads();
-        // ---- phase B: A p' (S4:526-535) marching down the thread's rows: p' of the rows above and below and the flux through
-        // the upper face stay in registers (the flux through a face is one expression for both cells that share it)
+        // ---- phase B: A p' (S4:526-535) marching down the thread's rows: p' of the current row and the fluxes through its
+        // upper faces stay in registers; the flux through a face is one expression for both cells that share it, so the
+        // face between the pair's two cells is computed once
         double s1[1] = {0.0};
         if (work && r0 < r1) {
-            int ip = (r0 + 1) * PC + txc + 1, ic = r0 * Ct + txc;
-            const size_t o_col = o00 + txc + 1;
-            double pd = sP[ip - PC], pc = sP[ip];
-            bool bad_c = out_of_div_range(pc) != 0u;
-            double fx_lo;
+            int ip = ip0, ic = ic0;
+            size_t og = og0;
+            const double2 pd = lds2(sP + ip - PC);
+            double2 pc = lds2(sP + ip);
+            bool bad_c = (out_of_div_range(pc.x) | out_of_div_range(pc.y)) != 0u;
+            double fxl0, fxl1;
             {
-                const unsigned K = sK[ic];
-                const double a_c = tl_coef(K & 3u, inv_eps, A.a + o_col + (size_t)(r0 + 1) * P);
-                const double num = a_c * (pc - pd);
-                if (__any_sync(0xffffffffu, safe || bad_c || out_of_div_range(pd) != 0u)) fx_lo = __ddiv_rn(num, h1);
-                else fx_lo = pw1 ? __dmul_rn(num, rh1) : div_const_nocheck(num, h1, rh1);
+                const unsigned K2 = *reinterpret_cast<const unsigned short *>(sK + ic);
+                const double a0 = tl_coef(K2 & 3u, inv_eps, A.a + og), a1 = tl_coef((K2 >> 8) & 3u, inv_eps, A.a + og + 1);
+                const double n0 = a0 * (pc.x - pd.x), n1 = a1 * (pc.y - pd.y);
+                if (__any_sync(0xffffffffu, safe || bad_c || (out_of_div_range(pd.x) | out_of_div_range(pd.y)) != 0u)) {
+                    fxl0 = __ddiv_rn(n0, h1);
+                    fxl1 = __ddiv_rn(n1, h1);
+                } else {
+                    fxl0 = pw1 ? __dmul_rn(n0, rh1) : div_const_nocheck(n0, h1, rh1);
+                    fxl1 = pw1 ? __dmul_rn(n1, rh1) : div_const_nocheck(n1, h1, rh1);
+                }
             }
-            for (int r = r0; r < r1; ++r, ip += PC, ic += Ct) {
-                const double pu = sP[ip + PC], pl = sP[ip - 1], pr = sP[ip + 1];
-                const unsigned K = sK[ic];
-                const bool bad_u = out_of_div_range(pu) != 0u;
-                const bool bad_e = out_of_div_range(lane == 0 ? pl : pr) != 0u; // the neighbours outside this warp (inside: bad_c of the lanes)
+            for (int r = r0; r < r1; ++r, ip += PC, ic += Cp, og += P) {
+                const double2 pu = lds2(sP + ip + PC);
+                const double pl = sP[ip - 1], pr = sP[ip + 2];
+                const unsigned K2 = *reinterpret_cast<const unsigned short *>(sK + ic), K0 = K2 & 0xffu, K1 = K2 >> 8;
+                const bool bad_u = (out_of_div_range(pu.x) | out_of_div_range(pu.y)) != 0u;
+                const bool bad_e = out_of_div_range(lane == 0 ? pl : pr) != 0u; // the neighbours outside this warp (inside: the lanes' own cells)
                 const bool slow = __any_sync(0xffffffffu, safe || bad_c || bad_u || bad_e);
-                double a_u, b_c, b_r;
-                if (__any_sync(0xffffffffu, (K & 0xa8u) != 0u)) { // a cell cut by the ellipse: its exact coefficient
-                    const size_t o = o_col + (size_t)(r + 1) * P;
-                    a_u = tl_coef((K >> 2) & 3u, inv_eps, A.a + o + P);
-                    b_c = tl_coef((K >> 4) & 3u, inv_eps, A.b + o);
-                    b_r = tl_coef((K >> 6) & 3u, inv_eps, A.b + o + 1);
+                double au0, au1, bc0, bm, br1; // a above the two cells; b left of the pair, between its cells, right of it
+                if (__any_sync(0xffffffffu, ((K0 | K1) & 0xa8u) != 0u)) { // a cell cut by the ellipse: its exact coefficient
+                    au0 = tl_coef((K0 >> 2) & 3u, inv_eps, A.a + og + P);
+                    au1 = tl_coef((K1 >> 2) & 3u, inv_eps, A.a + og + P + 1);
+                    bc0 = tl_coef((K0 >> 4) & 3u, inv_eps, A.b + og);
+                    bm = tl_coef((K0 >> 6) & 3u, inv_eps, A.b + og + 1);
+                    br1 = tl_coef((K1 >> 6) & 3u, inv_eps, A.b + og + 2);
                 } else {
-                    a_u = (K & 0x04u) ? inv_eps : 1.0;
-                    b_c = (K & 0x10u) ? inv_eps : 1.0;
-                    b_r = (K & 0x40u) ? inv_eps : 1.0;
+                    au0 = (K0 & 0x04u) ? inv_eps : 1.0;
+                    au1 = (K1 & 0x04u) ? inv_eps : 1.0;
+                    bc0 = (K0 & 0x10u) ? inv_eps : 1.0;
+                    bm = (K0 & 0x40u) ? inv_eps : 1.0;
+                    br1 = (K1 & 0x40u) ? inv_eps : 1.0;
                 }
-                const double nxu = a_u * (pu - pc), nyh = b_r * (pr - pc), nyl = b_c * (pc - pl); // S4:527, 531
-                double fx_hi, fy_hi, fy_lo;
+                const double nx0 = au0 * (pu.x - pc.x), nx1 = au1 * (pu.y - pc.y);                                  // S4:527
+                const double nl = bc0 * (pc.x - pl), nm = bm * (pc.y - pc.x), nr = br1 * (pr - pc.y);                // S4:531
+                double fxh0, fxh1, fl, fm, fr;
                 if (slow) {
-                    fx_hi = __ddiv_rn(nxu, h1);
-                    fy_hi = __ddiv_rn(nyh, h2);
-                    fy_lo = __ddiv_rn(nyl, h2);
+                    fxh0 = __ddiv_rn(nx0, h1);
+                    fxh1 = __ddiv_rn(nx1, h1);
+                    fl = __ddiv_rn(nl, h2);
+                    fm = __ddiv_rn(nm, h2);
+                    fr = __ddiv_rn(nr, h2);
                 } else {
-                    fx_hi = pw1 ? __dmul_rn(nxu, rh1) : div_const_nocheck(nxu, h1, rh1);
-                    fy_hi = pw2 ? __dmul_rn(nyh, rh2) : div_const_nocheck(nyh, h2, rh2);
-                    fy_lo = pw2 ? __dmul_rn(nyl, rh2) : div_const_nocheck(nyl, h2, rh2);
+                    fxh0 = pw1 ? __dmul_rn(nx0, rh1) : div_const_nocheck(nx0, h1, rh1);
+                    fxh1 = pw1 ? __dmul_rn(nx1, rh1) : div_const_nocheck(nx1, h1, rh1);
+                    fl = pw2 ? __dmul_rn(nl, rh2) : div_const_nocheck(nl, h2, rh2);
+                    fm = pw2 ? __dmul_rn(nm, rh2) : div_const_nocheck(nm, h2, rh2);
+                    fr = pw2 ? __dmul_rn(nr, rh2) : div_const_nocheck(nr, h2, rh2);
                 }
-                const double Ap = mih1 * (fx_hi - fx_lo) + mih2 * (fy_hi - fy_lo); // S4:526-535
-                if (own) {
-                    sAp[ic] = Ap;
-                    s1[0] += Ap * pc; // S4:594
+                const double Ap0 = mih1 * (fxh0 - fxl0) + mih2 * (fm - fl); // S4:526-535
+                const double Ap1 = mih1 * (fxh1 - fxl1) + mih2 * (fr - fm);
+                if (own0) {
+                    sts2(sAp + ic, Ap0, Ap1, own1);
+                    s1[0] += Ap0 * pc.x; // S4:594
+                    if (own1) s1[0] += Ap1 * pc.y;
                 }
-                pd = pc;
                 pc = pu;
                 bad_c = bad_u;
-                fx_lo = fx_hi;
+                fxl0 = fxh0;
+                fxl1 = fxh1;
             }
         }
         if (!tile_allreduce<1>(s1, A, (unsigned)(2 * k - 1), 1u, false, s_red, s_words, s_bc, &s_fail)) {
@@ -356,39 +408,64 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
             status = STOP_DENOM;
             break;
         }
-        // ---- phase C: the updates and the two sums
+        // ---- phase C: the updates and the two sums; w of the next row is requested before this row is worked on
         alpha = zr_old / denom; // S4:877
         double s2[2] = {0.0, 0.0};
         if (work && r0 < r1) {
-            int ip = (r0 + 1) * PC + txc + 1, ic = r0 * Ct + txc;
-            size_t o = o00 + (size_t)(r0 + 1) * P + txc + 1;
-            const int lj = j_lo + txc;
-            for (int r = r0; r < r1; ++r, ip += PC, ic += Ct, o += P) {
-                const double w0 = __ldcg(&A.w[o]);
-                const double pc = sP[ip];
-                const double wn = w0 + alpha * pc;          // S4:647
-                const double rn = sR[ic] - alpha * sAp[ic]; // S4:648
-                const double d = wn - w0;                   // S4:653
-                const unsigned kd = sD[ip];
-                const double2 DR = s_lut[kd];
-                double z;
-                if (__any_sync(0xffffffffu, safe || kd == DCLS_GENERAL || !in_div_range(rn)))
-                    z = precond_div(rn, kd == DCLS_GENERAL ? __ldg(A.D + o) : DR.x); // S4:559
-                else
-                    z = div_const_nocheck(rn, DR.x, DR.y);
-                if (own) {
-                    __stcg(&A.w[o], wn);
-                    sR[ic] = rn;
-                    s2[0] += d * d;
-                    s2[1] += z * rn; // S4:594
-                    if (r == 0 || r == Rt - 1 || txc == 0 || txc == Ct - 1) { // the neighbouring tiles' halo (S4:361-398)
-                        __stcg(&A.r[o], rn);
-                        if (A.c.multi == 2) { // ... and the neighbouring GPUs' rings, through NVLink
+            int ip = ip0, ic = ic0;
+            size_t og = og0;
+            const int lj = j_lo + c0;
+            const bool col_edge0 = c0 == 0 || c0 == Ct - 1, col_edge1 = c0 + 1 == Ct - 1; // first / last column of the tile
+            double wa = own0 ? __ldcg(&A.w[og]) : 0.0, wb = own1 ? __ldcg(&A.w[og + 1]) : 0.0;
+            for (int r = r0; r < r1; ++r, ip += PC, ic += Cp, og += P) {
+                const double w0 = wa, w1 = wb;
+                if (r + 1 < r1) {
+                    wa = own0 ? __ldcg(&A.w[og + P]) : 0.0;
+                    wb = own1 ? __ldcg(&A.w[og + P + 1]) : 0.0;
+                }
+                const double2 pc = lds2(sP + ip), rv = lds2(sR + ic), Ap = lds2(sAp + ic);
+                const double wn0 = w0 + alpha * pc.x, wn1 = w1 + alpha * pc.y;       // S4:647
+                const double rn0 = rv.x - alpha * Ap.x, rn1 = rv.y - alpha * Ap.y;   // S4:648
+                const double d0 = wn0 - w0, d1 = wn1 - w1;                           // S4:653
+                const unsigned kd2 = *reinterpret_cast<const unsigned short *>(sD + ip), kd0 = kd2 & 0xffu, kd1 = kd2 >> 8;
+                const double2 DR0 = s_lut[kd0], DR1 = s_lut[kd1];
+                double z0, z1;
+                if (__any_sync(0xffffffffu, safe || kd0 == DCLS_GENERAL || kd1 == DCLS_GENERAL || !in_div_range(rn0) || !in_div_range(rn1))) {
+                    z0 = precond_div(rn0, kd0 == DCLS_GENERAL ? __ldg(A.D + og) : DR0.x); // S4:559
+                    z1 = precond_div(rn1, kd1 == DCLS_GENERAL ? __ldg(A.D + og + 1) : DR1.x);
+                } else {
+                    z0 = div_const_nocheck(rn0, DR0.x, DR0.y);
+                    z1 = div_const_nocheck(rn1, DR1.x, DR1.y);
+                }
+                if (own0) {
+                    __stcg(&A.w[og], wn0);
+                    if (own1) __stcg(&A.w[og + 1], wn1);
+                    sts2(sR + ic, rn0, rn1, own1);
+                    s2[0] += d0 * d0;
+                    s2[1] += z0 * rn0; // S4:594
+                    if (own1) {
+                        s2[0] += d1 * d1;
+                        s2[1] += z1 * rn1;
+                    }
+                    const bool row_edge = r == 0 || r == Rt - 1;
+                    // the neighbouring tiles' halo (S4:361-398) and, on a block edge with a neighbour GPU, that GPU's ring (NVLink)
+                    if (row_edge || col_edge0) {
+                        __stcg(&A.r[og], rn0);
+                        if (A.c.multi == 2) {
                             const int li = i_lo + r;
-                            if (li == 1 && A.pv.r_left) A.pv.r_left[(size_t)(A.pv.nx_left + 1) * P + lj] = rn;
-                            if (li == g.nx && A.pv.r_right) A.pv.r_right[lj] = rn;
-                            if (lj == 1 && A.pv.r_down) A.pv.r_down[(size_t)li * A.pv.pitch_down + A.pv.ny_down + 1] = rn;
-                            if (lj == g.ny && A.pv.r_up) A.pv.r_up[(size_t)li * A.pv.pitch_up] = rn;
+                            if (li == 1 && A.pv.r_left) A.pv.r_left[(size_t)(A.pv.nx_left + 1) * P + lj] = rn0;
+                            if (li == g.nx && A.pv.r_right) A.pv.r_right[lj] = rn0;
+                            if (lj == 1 && A.pv.r_down) A.pv.r_down[(size_t)li * A.pv.pitch_down + A.pv.ny_down + 1] = rn0;
+                            if (lj == g.ny && A.pv.r_up) A.pv.r_up[(size_t)li * A.pv.pitch_up] = rn0;
+                        }
+                    }
+                    if (own1 && (row_edge || col_edge1)) {
+                        __stcg(&A.r[og + 1], rn1);
+                        if (A.c.multi == 2) {
+                            const int li = i_lo + r;
+                            if (li == 1 && A.pv.r_left) A.pv.r_left[(size_t)(A.pv.nx_left + 1) * P + lj + 1] = rn1;
+                            if (li == g.nx && A.pv.r_right) A.pv.r_right[lj + 1] = rn1;
+                            if (lj + 1 == g.ny && A.pv.r_up) A.pv.r_up[(size_t)li * A.pv.pitch_up] = rn1;
                         }
                     }
                 }
@@ -426,8 +503,8 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
     for (int q = tid; q < Rt * Ct; q += TL_THREADS) {
         const int lr = q / Ct, lc = q - lr * Ct;
         const size_t o = o00 + (size_t)(lr + 1) * P + (lc + 1);
-        A.r[o] = sR[q];
-        p_out[o] = sP[(lr + 1) * PC + (lc + 1)];
+        A.r[o] = sR[lr * Cp + lc];
+        p_out[o] = sP[(lr + 1) * PC + lc + 2];
     }
     if (bid == 0 && tid == 0) {
         Ctl *ctl = A.ctl;

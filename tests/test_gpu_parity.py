@@ -356,7 +356,7 @@ def test_resident_loop_and_two_kernel_paths_agree(monkeypatch, m, n, kw):
         np.testing.assert_allclose(w0, w1, rtol=0, atol=1e-12)
 
 
-@pytest.mark.parametrize("m,n,kw", [(2, 2, {}), (2, 300, {}), (300, 2, {}), (33, 1500, {}), (1500, 33, {}), (149, 1025, {}),
+@pytest.mark.parametrize("m,n,kw", [(2, 2, {}), (2, 300, {}), (300, 2, {}), (33, 1500, {}), (1500, 33, {}), (149, 1025, {}), (100, 140, {}), (96, 283, {}),
                                     (1000, 1300, {"fixed_iters": 60}), (1100, 1180, {"fixed_iters": 25}),
                                     (257, 130, {"eps": 1e-95, "fixed_iters": 12}), (130, 260, {"eps": 1e-3, "ell_ax": 0.7, "rhs_mode": 1})])
 def test_tile_loop_kernel_shapes(monkeypatch, oracle, m, n, kw):
