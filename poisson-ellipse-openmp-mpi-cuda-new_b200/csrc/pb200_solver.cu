@@ -267,8 +267,11 @@ bool tile_plan(int nx, int ny, int sms, size_t smem_max, int &R, int &C, int &tr
         const int Rq = (nx + r_try - 1) / r_try, Cq = (ny + c_try - 1) / c_try;
         if (Cq > TL_MAXC || 2 * (Rq + Cq) > TL_NH * TL_THREADS) continue;
         if (tile_smem_bytes(Rq, Cq) > smem_max) continue;
-        // cost: the largest tile's cells plus its halo ring (recomputed p'; column halos are strided global reads)
-        const double cost = static_cast<double>(Rq) * Cq + 2.0 * Cq + 6.0 * Rq;
+        // cost: what the slowest warp does per phase -- a thread owns a pair of columns and marches down its share of the
+        // rows (pb200_tile.cuh) -- times the warps that share the SM's issue slots, plus the halo ring (one p' each)
+        const int npair = (Cq + 1) / 2, txp = ((npair + 31) / 32) * 32, ty = std::max(1, std::min(TL_THREADS / txp, Rq));
+        const int rows_per_thread = (Rq + ty - 1) / ty, warps = ty * txp / 32;
+        const double cost = static_cast<double>(rows_per_thread) * std::max(4, warps) + (2.0 * Cq + 2.0 * Rq) / 64.0;
         if (cost < best) {
             best = cost;
             R = Rq;

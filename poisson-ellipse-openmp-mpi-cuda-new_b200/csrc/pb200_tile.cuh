@@ -63,13 +63,101 @@ struct TileArgs {
 //   sD   bytes indexed like sP: diagonal class;   sK   bytes indexed like sR: the coefficient classes of the cell's stencil
 __host__ __device__ inline int tile_pc(int C) { return (C + 4 + 1) & ~1; }
 __host__ __device__ inline int tile_cp(int C) { return (C + 1) & ~1; }
+//   sHv, sHk   a hash table of TL_HASH exact values: the a, b, D of the cells cut by the ellipse ("general" class), so that the
+//        loop never waits for global memory (the gpu-scope fences of the all-reduce empty the L1 every iteration)
+constexpr int TL_HASH = 2048, TL_HASH_BITS = 11, TL_PROBES = 24;
 __host__ __device__ inline size_t tile_smem_bytes(int R, int C) {
     const size_t halo = (size_t)(R + 2) * (size_t)tile_pc(C), own = (size_t)R * (size_t)tile_cp(C);
-    return (halo + 2 * own) * sizeof(double) + ((halo + 15) / 16) * 16 + ((own + 15) / 16) * 16;
+    return (halo + 2 * own) * sizeof(double) + ((halo + 15) / 16) * 16 + ((own + 15) / 16) * 16 + TL_HASH * (sizeof(double) + sizeof(unsigned));
+}
+
+// key of an exact value: field 0 = D of the cell at haloed index i and 4 = RN(1/D), 1 = a of the cell above compact index i,
+// 2 = b of the cell itself, 3 = b of the cell right of it
+__device__ __forceinline__ unsigned tl_key(int index, unsigned field) { return ((unsigned)(index + 1) << 3) | field; }
+__device__ __forceinline__ unsigned tl_hash(unsigned key) { return (key * 2654435761u) >> (32 - TL_HASH_BITS); }
+__device__ __forceinline__ void tl_insert(unsigned *keys, double *vals, unsigned key, double v) {
+    unsigned slot = tl_hash(key);
+    for (int probe = 0; probe < TL_PROBES; ++probe) {
+        const unsigned old = atomicCAS(&keys[slot], 0u, key);
+        if (old == 0u || old == key) {
+            vals[slot] = v;
+            return;
+        }
+        slot = (slot + 1u) & (TL_HASH - 1);
+    }
+    // table full around here: the value stays in global memory only (tl_lookup falls back to it)
+}
+__device__ __forceinline__ double tl_lookup(const unsigned *keys, const double *vals, unsigned key, const double *global_cell) {
+    unsigned slot = tl_hash(key);
+    for (int probe = 0; probe < TL_PROBES; ++probe) {
+        const unsigned kk = keys[slot];
+        if (kk == key) return vals[slot];
+        if (kk == 0u) break;
+        slot = (slot + 1u) & (TL_HASH - 1);
+    }
+    return __ldg(global_cell);
+}
+// (D, RN(1/D)) of a cell whose diagonal is not in the class table; false: not in the table (it was full)
+__device__ __forceinline__ bool tl_lookup_diag(const unsigned *keys, const double *vals, int index, double2 &DR) {
+    const unsigned kD = tl_key(index, 0u), kR = tl_key(index, 4u);
+    unsigned sD = tl_hash(kD), sR = tl_hash(kR);
+    bool fD = false, fR = false;
+    for (int probe = 0; probe < TL_PROBES && !(fD && fR); ++probe) {
+        if (!fD) {
+            const unsigned kk = keys[sD];
+            if (kk == kD) {
+                DR.x = vals[sD];
+                fD = true;
+            } else if (kk == 0u) return false;
+            else sD = (sD + 1u) & (TL_HASH - 1);
+        }
+        if (!fR) {
+            const unsigned kk = keys[sR];
+            if (kk == kR) {
+                DR.y = vals[sR];
+                fR = true;
+            } else if (kk == 0u) return false;
+            else sR = (sR + 1u) & (TL_HASH - 1);
+        }
+    }
+    return fD && fR;
+}
+// z = D^-1 r (S4:559) for a thread's pair of cells. The exact-residual division needs D with its correctly rounded
+// reciprocal -- from the class table, or from the hash table for a cell next to the ellipse boundary (Markstein's theorem
+// holds for any divisor; tests/test_gpu_parity.py runs pb200_selftest_div on such diagonals) -- and r inside the window
+// (in_div_range). Anything else -- warp-wide, so that no lane waits for another's IEEE division alone -- divides as the
+// reference does.
+__device__ __forceinline__ void tl_precond2(double r0, double r1, unsigned kd0, unsigned kd1, const double2 *lut,
+                                            const unsigned *keys, const double *vals, int ip, const double *D_cell,
+                                            bool safe, double &z0, double &z1) {
+    double2 DR0 = lut[kd0], DR1 = lut[kd1];
+    bool slow = safe || !in_div_range(r0) || !in_div_range(r1);
+    if (__any_sync(0xffffffffu, kd0 == DCLS_GENERAL || kd1 == DCLS_GENERAL)) {
+        if (kd0 == DCLS_GENERAL && !tl_lookup_diag(keys, vals, ip, DR0)) {
+            DR0.x = __ldg(D_cell);
+            slow = true;
+        }
+        if (kd1 == DCLS_GENERAL && !tl_lookup_diag(keys, vals, ip + 1, DR1)) {
+            DR1.x = __ldg(D_cell + 1);
+            slow = true;
+        }
+    }
+    if (__any_sync(0xffffffffu, slow)) {
+        z0 = precond_div(r0, DR0.x);
+        z1 = precond_div(r1, DR1.x);
+    } else {
+        z0 = div_const_nocheck(r0, DR0.x, DR0.y);
+        z1 = div_const_nocheck(r1, DR1.x, DR1.y);
+    }
 }
 
 __device__ __forceinline__ double tl_coef(unsigned k, double inv_eps, const double *cell) {
     return (k == 0u) ? 1.0 : ((k == 1u) ? inv_eps : __ldg(cell));
+}
+// release / acquire fences of the all-reduce (acq_rel is enough for the message-passing pattern; __threadfence() is sc)
+__device__ __forceinline__ void tl_fence(bool sys) {
+    if (sys) asm volatile("fence.acq_rel.sys;" ::: "memory");
+    else asm volatile("fence.acq_rel.gpu;" ::: "memory");
 }
 
 // class byte of stored cell (li, lj) from the per-window class map (cls_store)
@@ -113,7 +201,12 @@ __device__ __forceinline__ unsigned tl_poll(const unsigned long long *p, unsigne
 template <int NV>
 __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &A, const unsigned gen, const unsigned wmask,
                                                const bool publish, double (*s_red)[TL_THREADS / 32], unsigned (*s_words)[TL_MAX_BLOCKS],
-                                               double *s_bc, int *s_fail) {
+                                               double *s_bc, int *s_fail, long long *stamp = nullptr) {
+#ifdef PB200_TILE_TIMING
+#define AR_STAMP(i) if (stamp) stamp[i] = clock64()
+#else
+#define AR_STAMP(i)
+#endif
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nblocks = gridDim.x, bid = blockIdx.x;
     const bool sys = A.c.multi == 2;
@@ -122,24 +215,26 @@ __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &
         const double s = warp_sum(v[k]);
         if (lane == 0) s_red[k][warp] = s;
     }
+    AR_STAMP(0);
     __syncthreads();
+    AR_STAMP(1);
     if (tid < 2 * NV) { // one thread per word: the CTA's sum of value tid / 2, warps in index order
         const int k = tid >> 1;
         double s = 0.0;
 #pragma unroll
         for (int q = 0; q < TL_THREADS / 32; ++q) s += s_red[k][q];
-        if (publish) {
-            if (sys) __threadfence_system(); // edge cells may have gone to a peer GPU
-            else __threadfence();
-        }
+        if (publish) tl_fence(sys); // release: the r of the edge cells (they may have gone to a peer GPU)
         *reinterpret_cast<volatile unsigned long long *>(&A.slots[(2 * k + (tid & 1)) * TL_MAX_BLOCKS + bid]) = tl_word(s, tid & 1, gen);
     }
+    AR_STAMP(2);
     if (bid == 0) { // gather the CTAs' partials, add them in CTA order, post the GPU's totals to every GPU
         for (int i = tid; i < 2 * NV * nblocks; i += TL_THREADS) {
             const int kh = i / nblocks, b = i - kh * nblocks;
             s_words[kh][b] = tl_poll(&A.slots[kh * TL_MAX_BLOCKS + b], gen, s_fail);
         }
+        AR_STAMP(3);
         __syncthreads();
+        AR_STAMP(4);
         if (warp == 0) {
             double tot[NV];
 #pragma unroll
@@ -150,10 +245,7 @@ __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &
                 s = ((wmask >> k) & 1u) ? s * A.c.h1 * A.c.h2 : s; // S3:191: sum * h1 * h2
                 tot[k] = __shfl_sync(0xffffffffu, s, 0);
             }
-            if (publish) {
-                if (sys) __threadfence_system();
-                else __threadfence();
-            }
+            if (publish) tl_fence(sys);
             const int nw = A.pv.nranks * 2 * NV; // lane -> (destination rank, value, half)
             if (lane < nw) {
                 const int q = lane / (2 * NV), kh = lane - q * (2 * NV);
@@ -163,6 +255,7 @@ __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &
             }
         }
     }
+    AR_STAMP(5);
     if (warp == 0) { // every CTA: this GPU's mailbox, all ranks' totals, added in rank order
         const int nw = A.pv.nranks * 2 * NV;
         unsigned pay = 0u;
@@ -172,10 +265,8 @@ __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &
             pay = tl_poll(src, gen, s_fail);
         }
         __syncwarp();
-        if (publish) {
-            if (sys) __threadfence_system();
-            else __threadfence();
-        }
+        AR_STAMP(6);
+        if (publish) tl_fence(sys); // acquire
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
             double s = 0.0;
@@ -187,6 +278,7 @@ __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &
         }
     }
     __syncthreads();
+    AR_STAMP(7);
 #pragma unroll
     for (int k = 0; k < NV; ++k) v[k] = s_bc[k];
     return *reinterpret_cast<volatile int *>(s_fail) == 0;
@@ -221,6 +313,8 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
     double *sAp = sR + n_own;
     unsigned char *sD = reinterpret_cast<unsigned char *>(sAp + n_own);
     unsigned char *sK = sD + ((n_halo + 15) / 16) * 16; // a(c) | a(up) << 2 | b(c) << 4 | b(right) << 6
+    double *sHv = reinterpret_cast<double *>(sK + ((n_own + 15) / 16) * 16);
+    unsigned *sHk = reinterpret_cast<unsigned *>(sHv + TL_HASH);
     const int P = g.pitch;
     const size_t o00 = (size_t)(i_lo - 1) * P + (size_t)(j_lo - 1); // global offset of the tile's halo corner (row i_lo-1, column j_lo-1)
     const bool safe = A.safe != 0;
@@ -238,17 +332,28 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
         sAp[q] = 0.0;
         sK[q] = 0;
     }
+    for (int q = tid; q < TL_HASH; q += TL_THREADS) sHk[q] = 0u;
     __syncthreads();
     for (int q = tid; q < (Rt + 2) * (Ct + 2); q += TL_THREADS) { // halo coordinates (hr, hc): row i_lo-1+hr, column j_lo-1+hc
         const int hr = q / (Ct + 2), hc = q - hr * (Ct + 2);
-        sD[hr * PC + hc + 1] = (unsigned char)(tl_class(A.cls, g.cpitch, i_lo - 1 + hr, j_lo - 1 + hc) >> 4);
+        const unsigned kd = tl_class(A.cls, g.cpitch, i_lo - 1 + hr, j_lo - 1 + hc) >> 4;
+        sD[hr * PC + hc + 1] = (unsigned char)kd;
+        if (kd == DCLS_GENERAL) {
+            const double vD = A.D[o00 + (size_t)hr * P + hc];
+            tl_insert(sHk, sHv, tl_key(hr * PC + hc + 1, 0u), vD);
+            tl_insert(sHk, sHv, tl_key(hr * PC + hc + 1, 4u), 1.0 / vD);
+        }
     }
     for (int q = tid; q < Rt * Ct; q += TL_THREADS) {
         const int lr = q / Ct, lc = q - lr * Ct, li = i_lo + lr, lj = j_lo + lc;
         const unsigned kc = tl_class(A.cls, g.cpitch, li, lj), ku = tl_class(A.cls, g.cpitch, li + 1, lj),
                        kr = tl_class(A.cls, g.cpitch, li, lj + 1);
         sK[lr * Cp + lc] = (unsigned char)((kc & 3u) | ((ku & 3u) << 2) | (((kc >> 2) & 3u) << 4) | (((kr >> 2) & 3u) << 6));
-        sR[lr * Cp + lc] = A.r[(size_t)li * P + lj]; // S4:813: r = B (setup / reset kernel)
+        const size_t o = (size_t)li * P + lj;
+        if ((ku & 3u) == CLS_GENERAL) tl_insert(sHk, sHv, tl_key(lr * Cp + lc, 1u), A.a[o + P]);
+        if (((kc >> 2) & 3u) == CLS_GENERAL) tl_insert(sHk, sHv, tl_key(lr * Cp + lc, 2u), A.b[o]);
+        if (((kr >> 2) & 3u) == CLS_GENERAL) tl_insert(sHk, sHv, tl_key(lr * Cp + lc, 3u), A.b[o + 1]);
+        sR[lr * Cp + lc] = A.r[o]; // S4:813: r = B (setup / reset kernel)
     }
     // Thread layout: a thread owns a PAIR of adjacent columns and marches down its rows; when the tile is narrow, TY groups
     // of threads share the rows. Lanes past the last pair shadow it (same reads, no stores, nothing summed), so that every
@@ -281,9 +386,17 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
     int status = STOP_MAX_ITER, conv_iter = 0;
     const int ip0 = (r0 + 1) * PC + c0 + 2, ic0 = r0 * Cp + c0;  // the pair's first cell in the haloed / compact arrays
     const size_t og0 = o00 + (size_t)(r0 + 1) * P + c0 + 1;      // ... and in global memory
+#ifdef PB200_TILE_TIMING // variant builds only (make variant): cycle stamps of one CTA's thread 0 instead of the scalar trace
+    const bool t_rec = A.trace && tid == 0 && (PB200_TILE_TIMING == 5 || bid == ((PB200_TILE_TIMING & 1) ? gridDim.x - 1u : 0u));
+    long long t_s[7], t_a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define TL_STAMP(i) t_s[i] = clock64()
+#else
+#define TL_STAMP(i)
+#endif
     for (;;) {
         ++k; // S4:847-848
         const bool first = k == 1;
+        TL_STAMP(0);
         // ---- phase A: p' = D^-1 r + beta p' (S4:559, 675; first: p = z, S4:830) on the halo ring -- its r comes from global
         // memory: ask for it first -- and on the own cells
         double r_halo[TL_NH];
@@ -295,15 +408,8 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
             for (int r = r0; r < r1; ++r, ip += PC, ic += Cp, og += P) {
                 const double2 rv = lds2(sR + ic);
                 const unsigned kd2 = *reinterpret_cast<const unsigned short *>(sD + ip), kd0 = kd2 & 0xffu, kd1 = kd2 >> 8;
-                const double2 DR0 = s_lut[kd0], DR1 = s_lut[kd1];
                 double z0, z1;
-                if (__any_sync(0xffffffffu, safe || kd0 == DCLS_GENERAL || kd1 == DCLS_GENERAL || !in_div_range(rv.x) || !in_div_range(rv.y))) {
-                    z0 = precond_div(rv.x, kd0 == DCLS_GENERAL ? __ldg(A.D + og) : DR0.x);
-                    z1 = precond_div(rv.y, kd1 == DCLS_GENERAL ? __ldg(A.D + og + 1) : DR1.x);
-                } else {
-                    z0 = div_const_nocheck(rv.x, DR0.x, DR0.y);
-                    z1 = div_const_nocheck(rv.y, DR1.x, DR1.y);
-                }
+                tl_precond2(rv.x, rv.y, kd0, kd1, s_lut, sHk, sHv, ip, A.D + og, safe, z0, z1); // S4:559
                 if (!first) {
                     const double2 po = lds2(sP + ip);
                     z0 = z0 + beta * po.x;
@@ -320,11 +426,13 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
                 const double2 DR = s_lut[kd];
                 const double rv = r_halo[n];
                 double z;
-                if (safe || kd == DCLS_GENERAL || !in_div_range(rv)) z = precond_div(rv, kd == DCLS_GENERAL ? __ldg(A.D + o00 + h_gl[n]) : DR.x);
+                if (safe || kd == DCLS_GENERAL || !in_div_range(rv))
+                    z = precond_div(rv, kd == DCLS_GENERAL ? tl_lookup(sHk, sHv, tl_key(ip, 0u), A.D + o00 + h_gl[n]) : DR.x);
                 else z = div_const_nocheck(rv, DR.x, DR.y);
                 sP[ip] = first ? z : z + beta * sP[ip];
             }
         __syncthreads();
+        TL_STAMP(1);
         // ---- phase B: A p' (S4:526-535) marching down the thread's rows: p' of the current row and the fluxes through its
         // upper faces stay in registers; the flux through a face is one expression for both cells that share it, so the
         // face between the pair's two cells is computed once
@@ -357,11 +465,11 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
                 const bool slow = __any_sync(0xffffffffu, safe || bad_c || bad_u || bad_e);
                 double au0, au1, bc0, bm, br1; // a above the two cells; b left of the pair, between its cells, right of it
                 if (__any_sync(0xffffffffu, ((K0 | K1) & 0xa8u) != 0u)) { // a cell cut by the ellipse: its exact coefficient
-                    au0 = tl_coef((K0 >> 2) & 3u, inv_eps, A.a + og + P);
-                    au1 = tl_coef((K1 >> 2) & 3u, inv_eps, A.a + og + P + 1);
-                    bc0 = tl_coef((K0 >> 4) & 3u, inv_eps, A.b + og);
-                    bm = tl_coef((K0 >> 6) & 3u, inv_eps, A.b + og + 1);
-                    br1 = tl_coef((K1 >> 6) & 3u, inv_eps, A.b + og + 2);
+                    au0 = (K0 & 0x08u) ? tl_lookup(sHk, sHv, tl_key(ic, 1u), A.a + og + P) : ((K0 & 0x04u) ? inv_eps : 1.0);
+                    au1 = (K1 & 0x08u) ? tl_lookup(sHk, sHv, tl_key(ic + 1, 1u), A.a + og + P + 1) : ((K1 & 0x04u) ? inv_eps : 1.0);
+                    bc0 = (K0 & 0x20u) ? tl_lookup(sHk, sHv, tl_key(ic, 2u), A.b + og) : ((K0 & 0x10u) ? inv_eps : 1.0);
+                    bm = (K0 & 0x80u) ? tl_lookup(sHk, sHv, tl_key(ic, 3u), A.b + og + 1) : ((K0 & 0x40u) ? inv_eps : 1.0);
+                    br1 = (K1 & 0x80u) ? tl_lookup(sHk, sHv, tl_key(ic + 1, 3u), A.b + og + 2) : ((K1 & 0x40u) ? inv_eps : 1.0);
                 } else {
                     au0 = (K0 & 0x04u) ? inv_eps : 1.0;
                     au1 = (K1 & 0x04u) ? inv_eps : 1.0;
@@ -398,10 +506,17 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
                 fxl1 = fxh1;
             }
         }
+        TL_STAMP(2);
+#ifdef PB200_TILE_TIMING
+        long long t_a1[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if (!tile_allreduce<1>(s1, A, (unsigned)(2 * k - 1), 1u, false, s_red, s_words, s_bc, &s_fail, t_rec ? t_a1 : nullptr)) {
+#else
         if (!tile_allreduce<1>(s1, A, (unsigned)(2 * k - 1), 1u, false, s_red, s_words, s_bc, &s_fail)) {
+#endif
             status = STOP_COMM_TIMEOUT;
             break;
         }
+        TL_STAMP(3);
         denom = s1[0]; // S4:866-872
         const bool brk = (c.norm_mode == 1) ? (denom < 1e-15) : (fabs(denom) < 1e-15); // S0:128 | S4:876
         if (brk) {
@@ -428,15 +543,8 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
                 const double rn0 = rv.x - alpha * Ap.x, rn1 = rv.y - alpha * Ap.y;   // S4:648
                 const double d0 = wn0 - w0, d1 = wn1 - w1;                           // S4:653
                 const unsigned kd2 = *reinterpret_cast<const unsigned short *>(sD + ip), kd0 = kd2 & 0xffu, kd1 = kd2 >> 8;
-                const double2 DR0 = s_lut[kd0], DR1 = s_lut[kd1];
                 double z0, z1;
-                if (__any_sync(0xffffffffu, safe || kd0 == DCLS_GENERAL || kd1 == DCLS_GENERAL || !in_div_range(rn0) || !in_div_range(rn1))) {
-                    z0 = precond_div(rn0, kd0 == DCLS_GENERAL ? __ldg(A.D + og) : DR0.x); // S4:559
-                    z1 = precond_div(rn1, kd1 == DCLS_GENERAL ? __ldg(A.D + og + 1) : DR1.x);
-                } else {
-                    z0 = div_const_nocheck(rn0, DR0.x, DR0.y);
-                    z1 = div_const_nocheck(rn1, DR1.x, DR1.y);
-                }
+                tl_precond2(rn0, rn1, kd0, kd1, s_lut, sHk, sHv, ip, A.D + og, safe, z0, z1); // S4:559
                 if (own0) {
                     __stcg(&A.w[og], wn0);
                     if (own1) __stcg(&A.w[og + 1], wn1);
@@ -471,15 +579,47 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
                 }
             }
         }
+        TL_STAMP(4);
+#ifdef PB200_TILE_TIMING
+        if (!tile_allreduce<2>(s2, A, (unsigned)(2 * k), 2u, true, s_red, s_words, s_bc, &s_fail, t_rec ? t_a : nullptr)) {
+#else
         if (!tile_allreduce<2>(s2, A, (unsigned)(2 * k), 2u, true, s_red, s_words, s_bc, &s_fail)) {
+#endif
             status = STOP_COMM_TIMEOUT;
             break;
         }
+        TL_STAMP(5);
         // ---- the scalar tail (finalize_iteration), in every thread
         const double zr_new = s2[1]; // S4:920-926
         diff = (c.norm_mode == 0) ? sqrt(s2[0] * h1 * h2) : sqrt(s2[0]); // S3:449 | S0:154
         const bool conv = diff < c.delta;                                 // S4:899
+#ifdef PB200_TILE_TIMING
+        const bool tr = false;
+        if (t_rec && 2 * k <= c.trace_len) { // rows 2k-2, 2k-1: A, B, all-reduce 1 | C, all-reduce 2, (unused)
+            if (PB200_TILE_TIMING == 5) { // every CTA, iteration 30 only: row bid = A, B, all-reduce 1, C, all-reduce 2, tile cells
+                if (k == 30 && (int)bid < c.trace_len / 2) {
+                    A.trace[6 * bid + 0] = (double)(t_s[1] - t_s[0]);   // phase A, whole CTA
+                    A.trace[6 * bid + 1] = (double)(t_a1[1] - t_s[1]);  // phase B, whole CTA (to the all-reduce's first barrier)
+                    A.trace[6 * bid + 2] = (double)(t_s[3] - t_a1[1]);  // rest of all-reduce 1
+                    A.trace[6 * bid + 3] = (double)(t_a[1] - t_s[3]);   // phase C, whole CTA
+                    A.trace[6 * bid + 4] = (double)(t_s[5] - t_a[1]);   // rest of all-reduce 2
+                    A.trace[6 * bid + 5] = (double)(Rt * 10000 + Ct);
+                }
+            } else if (PB200_TILE_TIMING <= 2) {
+                for (int j = 0; j < 5; ++j) A.trace[6 * (k - 1) + j] = (double)(t_s[j + 1] - t_s[j]);
+                A.trace[6 * (k - 1) + 5] = (double)t_s[0];
+            } else { // inside all-reduce 2: entry->sync | ->posted | gather | ->all gathered | sum+mail | mailbox poll+exit
+                A.trace[6 * (k - 1) + 0] = (double)(t_a[1] - t_a[0]);
+                A.trace[6 * (k - 1) + 1] = (double)(t_a[2] - t_a[1]);
+                A.trace[6 * (k - 1) + 2] = (double)(t_a[3] - t_a[2]);
+                A.trace[6 * (k - 1) + 3] = (double)(t_a[4] - t_a[3]);
+                A.trace[6 * (k - 1) + 4] = (double)(t_a[5] - t_a[4]);
+                A.trace[6 * (k - 1) + 5] = (double)(t_a[7] - t_a[5]);
+            }
+        }
+#else
         const bool tr = A.trace && k <= c.trace_len && bid == 0 && tid == 0;
+#endif
         if (tr) {
             A.trace[3 * (k - 1) + 0] = alpha;
             A.trace[3 * (k - 1) + 1] = 0.0;
