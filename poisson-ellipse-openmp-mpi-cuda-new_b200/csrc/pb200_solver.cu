@@ -289,6 +289,10 @@ void Solver::plan_tile(int sms) {
     const char *env = std::getenv("PB200_TILE"), *env_loop = std::getenv("PB200_LOOP");
     if ((env && atoi(env) == 0) || (env_loop && atoi(env_loop) == 0)) return; // tuning / tests: the other kernels
     if (c.multi == 1) return; // NCCL mode exchanges between kernels: the marching kernels
+    // One GPU, tiny block: the register-resident loop kernel with a thread per cell is quicker (40 x 40: 7.8 against 10.1 us
+    // per iteration, 100 x 100: 7.7 against 9.6; 400 x 600: 16.3 against 13.6). PB200_TILE=2 keeps this kernel (tests).
+    const long long cells = static_cast<long long>(f.g.nx) * f.g.ny;
+    if (c.multi == 0 && use_loop && loop_cells == 1 && cells <= 60000 && !(env && atoi(env) == 2)) return;
     int coop = 0, smem_optin = 0;
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
     cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);

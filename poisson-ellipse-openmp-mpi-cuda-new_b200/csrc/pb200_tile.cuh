@@ -71,7 +71,7 @@ __host__ __device__ inline size_t tile_smem_bytes(int R, int C) {
     return (halo + 2 * own) * sizeof(double) + ((halo + 15) / 16) * 16 + ((own + 15) / 16) * 16 + TL_HASH * (sizeof(double) + sizeof(unsigned));
 }
 
-// key of an exact value: field 0 = D of the cell at haloed index i and 4 = RN(1/D), 1 = a of the cell above compact index i,
+// key of an exact value: field 0 = D of the cell at haloed index i, 1 = a of the cell above compact index i,
 // 2 = b of the cell itself, 3 = b of the cell right of it
 __device__ __forceinline__ unsigned tl_key(int index, unsigned field) { return ((unsigned)(index + 1) << 3) | field; }
 __device__ __forceinline__ unsigned tl_hash(unsigned key) { return (key * 2654435761u) >> (32 - TL_HASH_BITS); }
@@ -97,54 +97,18 @@ __device__ __forceinline__ double tl_lookup(const unsigned *keys, const double *
     }
     return __ldg(global_cell);
 }
-// (D, RN(1/D)) of a cell whose diagonal is not in the class table; false: not in the table (it was full)
-__device__ __forceinline__ bool tl_lookup_diag(const unsigned *keys, const double *vals, int index, double2 &DR) {
-    const unsigned kD = tl_key(index, 0u), kR = tl_key(index, 4u);
-    unsigned sD = tl_hash(kD), sR = tl_hash(kR);
-    bool fD = false, fR = false;
-    for (int probe = 0; probe < TL_PROBES && !(fD && fR); ++probe) {
-        if (!fD) {
-            const unsigned kk = keys[sD];
-            if (kk == kD) {
-                DR.x = vals[sD];
-                fD = true;
-            } else if (kk == 0u) return false;
-            else sD = (sD + 1u) & (TL_HASH - 1);
-        }
-        if (!fR) {
-            const unsigned kk = keys[sR];
-            if (kk == kR) {
-                DR.y = vals[sR];
-                fR = true;
-            } else if (kk == 0u) return false;
-            else sR = (sR + 1u) & (TL_HASH - 1);
-        }
-    }
-    return fD && fR;
-}
-// z = D^-1 r (S4:559) for a thread's pair of cells. The exact-residual division needs D with its correctly rounded
-// reciprocal -- from the class table, or from the hash table for a cell next to the ellipse boundary (Markstein's theorem
-// holds for any divisor; tests/test_gpu_parity.py runs pb200_selftest_div on such diagonals) -- and r inside the window
-// (in_div_range). Anything else -- warp-wide, so that no lane waits for another's IEEE division alone -- divides as the
-// reference does.
+// z = D^-1 r (S4:559) for a thread's pair of cells: the exact-residual division with (D, RN(1/D)) from the class table when
+// every r of the warp lies in the window it is proven for (in_div_range) and no cell of the warp sits next to the ellipse
+// boundary; otherwise the whole warp divides as the reference does, the boundary cells by their exact D from the hash
+// table. (Measured: dividing the boundary cells by a cached reciprocal instead saved instructions and cost 5 us per
+// iteration at 1200 x 800 -- two more table look-ups on the slowest warps' path.)
 __device__ __forceinline__ void tl_precond2(double r0, double r1, unsigned kd0, unsigned kd1, const double2 *lut,
                                             const unsigned *keys, const double *vals, int ip, const double *D_cell,
                                             bool safe, double &z0, double &z1) {
-    double2 DR0 = lut[kd0], DR1 = lut[kd1];
-    bool slow = safe || !in_div_range(r0) || !in_div_range(r1);
-    if (__any_sync(0xffffffffu, kd0 == DCLS_GENERAL || kd1 == DCLS_GENERAL)) {
-        if (kd0 == DCLS_GENERAL && !tl_lookup_diag(keys, vals, ip, DR0)) {
-            DR0.x = __ldg(D_cell);
-            slow = true;
-        }
-        if (kd1 == DCLS_GENERAL && !tl_lookup_diag(keys, vals, ip + 1, DR1)) {
-            DR1.x = __ldg(D_cell + 1);
-            slow = true;
-        }
-    }
-    if (__any_sync(0xffffffffu, slow)) {
-        z0 = precond_div(r0, DR0.x);
-        z1 = precond_div(r1, DR1.x);
+    const double2 DR0 = lut[kd0], DR1 = lut[kd1];
+    if (__any_sync(0xffffffffu, safe || !in_div_range(r0) || !in_div_range(r1) || kd0 == DCLS_GENERAL || kd1 == DCLS_GENERAL)) {
+        z0 = precond_div(r0, kd0 == DCLS_GENERAL ? tl_lookup(keys, vals, tl_key(ip, 0u), D_cell) : DR0.x);
+        z1 = precond_div(r1, kd1 == DCLS_GENERAL ? tl_lookup(keys, vals, tl_key(ip + 1, 0u), D_cell + 1) : DR1.x);
     } else {
         z0 = div_const_nocheck(r0, DR0.x, DR0.y);
         z1 = div_const_nocheck(r1, DR1.x, DR1.y);
@@ -178,11 +142,12 @@ __device__ __forceinline__ unsigned long long tl_word(double v, int half, unsign
 // wait until the word at p carries `tag`; returns its payload. *fail is set if it does not arrive within ~3 s.
 __device__ __forceinline__ unsigned tl_poll(const unsigned long long *p, unsigned tag, int *fail) {
     const volatile unsigned long long *q = reinterpret_cast<const volatile unsigned long long *>(p);
-    unsigned long long wv = *q;
+    auto ld = [q]() { return *q; };
+    unsigned long long wv = ld();
     if ((unsigned)wv != tag) {
         const long long t0 = clock64();
         int spins = 0;
-        while ((unsigned)(wv = *q) != tag) {
+        while ((unsigned)(wv = ld()) != tag) {
             if ((++spins & 63) == 0 && clock64() - t0 > 6000000000ll) {
                 *fail = 1;
                 break;
@@ -338,11 +303,7 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
         const int hr = q / (Ct + 2), hc = q - hr * (Ct + 2);
         const unsigned kd = tl_class(A.cls, g.cpitch, i_lo - 1 + hr, j_lo - 1 + hc) >> 4;
         sD[hr * PC + hc + 1] = (unsigned char)kd;
-        if (kd == DCLS_GENERAL) {
-            const double vD = A.D[o00 + (size_t)hr * P + hc];
-            tl_insert(sHk, sHv, tl_key(hr * PC + hc + 1, 0u), vD);
-            tl_insert(sHk, sHv, tl_key(hr * PC + hc + 1, 4u), 1.0 / vD);
-        }
+        if (kd == DCLS_GENERAL) tl_insert(sHk, sHv, tl_key(hr * PC + hc + 1, 0u), A.D[o00 + (size_t)hr * P + hc]);
     }
     for (int q = tid; q < Rt * Ct; q += TL_THREADS) {
         const int lr = q / Ct, lc = q - lr * Ct, li = i_lo + lr, lj = j_lo + lc;
