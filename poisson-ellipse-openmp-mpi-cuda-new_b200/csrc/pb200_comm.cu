@@ -189,6 +189,8 @@ struct PeerBlob {
     int nx, ny, pitch, pad;
     void *r_ptr, *mail_ptr;
     cudaIpcMemHandle_t h_r, h_mail;
+    void *t_ptr;            // tagged copy of r (resident loop kernel), null when the blocks do not fit that kernel
+    cudaIpcMemHandle_t h_t;
 };
 static_assert(sizeof(PeerBlob) <= 256, "blob fits the 256 bytes of the C ABI");
 } // namespace
@@ -213,6 +215,8 @@ pb200_status Solver::peer_export(uint8_t blob[256]) {
     b.mail_ptr = mail;
     CK(cudaIpcGetMemHandle(&b.h_r, f.r));
     CK(cudaIpcGetMemHandle(&b.h_mail, mail));
+    b.t_ptr = tile_r2;
+    if (tile_r2) CK(cudaIpcGetMemHandle(&b.h_t, tile_r2));
     std::memset(blob, 0, 256);
     std::memcpy(blob, &b, sizeof(b));
     return PB200_OK;
@@ -228,11 +232,13 @@ pb200_status Solver::peer_attach(const uint8_t *blobs, int nranks) {
         std::memcpy(&all[q], blobs + 256 * q, sizeof(PeerBlob));
         if (all[q].magic != 0x50423230 || all[q].rank != q) { set_error("peer_attach: blob %d is not rank %d's export", q, q); return PB200_ERR_INVALID; }
     }
-    auto map = [&](const PeerBlob &b, bool want_r, double **mail_out, double **r_out) -> pb200_status {
+    auto map = [&](const PeerBlob &b, bool want_r, double **mail_out, double **r_out, unsigned long long **t_out) -> pb200_status {
         *r_out = nullptr;
+        *t_out = nullptr;
         if (b.rank == prm.rank) {
             *mail_out = mail;
             *r_out = f.r;
+            *t_out = tile_r2;
         } else if (b.pid == me) { // a thread of this process: same address space
             if (b.dev != dev) {
                 cudaError_t e = cudaDeviceEnablePeerAccess(b.dev, 0);
@@ -241,6 +247,7 @@ pb200_status Solver::peer_attach(const uint8_t *blobs, int nranks) {
             }
             *mail_out = static_cast<double *>(b.mail_ptr);
             *r_out = static_cast<double *>(b.r_ptr);
+            *t_out = static_cast<unsigned long long *>(b.t_ptr);
         } else {
             void *pm = nullptr, *pr = nullptr;
             CK(cudaIpcOpenMemHandle(&pm, b.h_mail, cudaIpcMemLazyEnablePeerAccess));
@@ -250,6 +257,12 @@ pb200_status Solver::peer_attach(const uint8_t *blobs, int nranks) {
                 CK(cudaIpcOpenMemHandle(&pr, b.h_r, cudaIpcMemLazyEnablePeerAccess));
                 ipc_opened.push_back(pr);
                 *r_out = static_cast<double *>(pr);
+                if (b.t_ptr) {
+                    void *pt = nullptr;
+                    CK(cudaIpcOpenMemHandle(&pt, b.h_t, cudaIpcMemLazyEnablePeerAccess));
+                    ipc_opened.push_back(pt);
+                    *t_out = static_cast<unsigned long long *>(pt);
+                }
             }
         }
         return PB200_OK;
@@ -263,12 +276,13 @@ pb200_status Solver::peer_attach(const uint8_t *blobs, int nranks) {
     for (int q = 0; q < nranks; ++q) {
         const bool nb = (q == left || q == right || q == down || q == up);
         double *rq = nullptr;
-        pb200_status st = map(all[q], nb, &pv.mail[q], &rq);
+        unsigned long long *tq = nullptr;
+        pb200_status st = map(all[q], nb, &pv.mail[q], &rq, &tq);
         if (st != PB200_OK) return st;
-        if (q == left) { pv.r_left = rq; pv.nx_left = all[q].nx; }
-        if (q == right) pv.r_right = rq;
-        if (q == down) { pv.r_down = rq; pv.ny_down = all[q].ny; pv.pitch_down = all[q].pitch; }
-        if (q == up) { pv.r_up = rq; pv.pitch_up = all[q].pitch; }
+        if (q == left) { pv.r_left = rq; pv.t_left = tq; pv.nx_left = all[q].nx; }
+        if (q == right) { pv.r_right = rq; pv.t_right = tq; }
+        if (q == down) { pv.r_down = rq; pv.t_down = tq; pv.ny_down = all[q].ny; pv.pitch_down = all[q].pitch; }
+        if (q == up) { pv.r_up = rq; pv.t_up = tq; pv.pitch_up = all[q].pitch; }
     }
     peer_ready = true;
     c.multi = 2;

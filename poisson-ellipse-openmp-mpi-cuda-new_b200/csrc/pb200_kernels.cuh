@@ -121,6 +121,8 @@ struct PeerView {
     double *r_left, *r_right, *r_down, *r_up;   // neighbours' r arrays; null = no neighbour on that side
     int nx_left;                                // the left neighbour's ring row nx_left+1 receives my row 1
     int ny_down, pitch_down, pitch_up;          // the lower neighbour's ring column ny_down+1 receives my column 1
+    // the neighbours' tagged copies of r (pb200_tile.cuh: two 64-bit words per cell, same indexing as r); null as r_*
+    unsigned long long *t_left, *t_right, *t_down, *t_up;
 };
 
 // One thread: publish nv values (slots at offsets off[v]) for iteration k to every rank, then wait for everyone's and

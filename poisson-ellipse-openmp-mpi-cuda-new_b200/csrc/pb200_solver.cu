@@ -191,6 +191,7 @@ Solver::~Solver() {
     if (trace) cudaFree(trace);
     if (norms) cudaFree(norms);
     if (tile_slots) cudaFree(tile_slots);
+    if (tile_r2) cudaFree(tile_r2);
     if (h_ctl) cudaFreeHost(h_ctl);
     f.release();
     if (stream) cudaStreamDestroy(stream);
@@ -284,6 +285,15 @@ bool tile_plan(int nx, int ny, int sms, size_t smem_max, int &R, int &C, int &tr
     return found;
 }
 
+// Could this decomposition run the resident loop kernel? Decided on the LARGEST block of the decomposition, so that every
+// rank gets the same answer (a rank in that kernel and its neighbour in the marching kernels would wait for each other
+// for ever).
+bool Solver::tile_feasible(int sms, size_t smem_max, int &R, int &C) const {
+    const int nx_max = (prm.M - 1 + Px - 1) / Px, ny_max = (prm.N - 1 + Py - 1) / Py;
+    int tr = 0, tc = 0;
+    return tile_plan(nx_max, ny_max, std::min(sms, TL_MAX_BLOCKS), smem_max, R, C, tr, tc);
+}
+
 void Solver::plan_tile(int sms) {
     use_tile = false;
     const char *env = std::getenv("PB200_TILE"), *env_loop = std::getenv("PB200_LOOP");
@@ -302,11 +312,8 @@ void Solver::plan_tile(int sms) {
         return;
     }
     const size_t smem_max = static_cast<size_t>(smem_optin) - fa.sharedSizeBytes;
-    // Every rank must take the same decision (a rank in this kernel and its neighbour in the marching kernels would wait
-    // for each other for ever): it is taken on the LARGEST block of the decomposition, which is the same number everywhere.
-    const int nx_max = (prm.M - 1 + Px - 1) / Px, ny_max = (prm.N - 1 + Py - 1) / Py;
     int R = 0, C = 0, tr = 0, tc = 0;
-    if (!tile_plan(nx_max, ny_max, std::min(sms, TL_MAX_BLOCKS), smem_max, R, C, tr, tc)) return;
+    if (!tile_feasible(sms, smem_max, R, C) || !tile_r2) return;
     int R2 = 0, C2 = 0, tr2 = 0, tc2 = 0; // this rank's own block: its own best cut, else the largest block's tile size
     if (tile_plan(f.g.nx, f.g.ny, std::min(sms, TL_MAX_BLOCKS), smem_max, R2, C2, tr2, tc2)) {
         R = R2;
@@ -427,6 +434,18 @@ pb200_status Solver::create(const pb200_params &params) {
     CK(cudaMalloc(&part2, std::max(2 * nb2, 3 * nb3) * sizeof(double))); // norms_kernel: 3 partials per block
     CK(cudaMalloc(&norms, 8 * sizeof(double)));
     CK(cudaMalloc(&tile_slots, TL_SLOT_WORDS * sizeof(unsigned long long)));
+    { // the tagged copy of r, for decompositions whose blocks fit the resident loop kernel (before any peer export)
+        int sms = 148, smem_optin = 0, R = 0, C = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        cudaFuncAttributes fa{};
+        if (cudaFuncGetAttributes(&fa, tile_loop_kernel) == cudaSuccess && smem_optin > static_cast<int>(fa.sharedSizeBytes) &&
+            tile_feasible(sms, static_cast<size_t>(smem_optin) - fa.sharedSizeBytes, R, C)) {
+            CK(cudaMalloc(&tile_r2, 2 * f.elems * sizeof(unsigned long long)));
+            plan_launch(); // again, now that the kernel's halo buffer exists
+        } else
+            cudaGetLastError();
+    }
     if (!mail) { // the mailbox of the in-kernel all-reduce (peer_export hands it to the other ranks)
         CK(cudaMalloc(&mail, MAIL_DOUBLES * sizeof(double)));
         CK(cudaMemset(mail, 0, MAIL_DOUBLES * sizeof(double)));
@@ -581,6 +600,7 @@ pb200_status Solver::solve(pb200_result *res) {
     long long k = 1;
     if (use_tile) { // one cooperative launch per rank runs every iteration, halo and sums included (pb200_tile.cuh)
         CK(cudaMemsetAsync(tile_slots, 0, TL_SLOT_WORDS * sizeof(unsigned long long), stream));
+        CK(cudaMemsetAsync(tile_r2, 0, 2 * f.elems * sizeof(unsigned long long), stream));
         TileArgs ta{};
         ta.w = f.w;
         ta.r = f.r;
@@ -591,6 +611,7 @@ pb200_status Solver::solve(pb200_result *res) {
         ta.D = f.D;
         ta.cls = f.cls;
         ta.slots = tile_slots;
+        ta.r2 = tile_r2;
         ta.trace = trace;
         ta.ctl = ctl;
         ta.g = f.g;

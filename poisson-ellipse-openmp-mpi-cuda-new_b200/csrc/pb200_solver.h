@@ -80,6 +80,8 @@ struct Solver {
     int tile_R = 0, tile_C = 0, tile_tr = 0, tile_tc = 0;
     size_t tile_smem = 0;
     unsigned long long *tile_slots = nullptr; // the CTAs' partial sums as tagged words
+    unsigned long long *tile_r2 = nullptr;    // tagged copy of r (2 words per cell): the halo of the resident loop kernel
+    bool tile_feasible(int sms, size_t smem_max, int &R, int &C) const; // on the largest block: the same answer on every rank
     long long launches = 0;
     long long last_iter = 0;
     double t_setup = 0.0;

@@ -47,6 +47,8 @@ struct TileArgs {
     const double *a, *b, *D;    // full arrays: read only where the class byte says "general"
     const unsigned char *cls;
     unsigned long long *slots;  // TL_SLOT_WORDS tagged words, zeroed before every solve
+    unsigned long long *r2;     // tagged copy of r, two words per stored cell (index 2 * (li * pitch + lj)), zeroed before every
+                                // solve: the tiles' edge cells travel through it (and through the neighbour GPUs' copies)
     double *trace;
     Ctl *ctl;
     Geom g;
@@ -118,12 +120,6 @@ __device__ __forceinline__ void tl_precond2(double r0, double r1, unsigned kd0, 
 __device__ __forceinline__ double tl_coef(unsigned k, double inv_eps, const double *cell) {
     return (k == 0u) ? 1.0 : ((k == 1u) ? inv_eps : __ldg(cell));
 }
-// release / acquire fences of the all-reduce (acq_rel is enough for the message-passing pattern; __threadfence() is sc)
-__device__ __forceinline__ void tl_fence(bool sys) {
-    if (sys) asm volatile("fence.acq_rel.sys;" ::: "memory");
-    else asm volatile("fence.acq_rel.gpu;" ::: "memory");
-}
-
 // class byte of stored cell (li, lj) from the per-window class map (cls_store)
 __device__ __forceinline__ unsigned tl_class(const unsigned char *cls, int cpitch, int li, int lj) {
     int w = lj / CLS_OWN, k = lj - w * CLS_OWN;
@@ -157,15 +153,38 @@ __device__ __forceinline__ unsigned tl_poll(const unsigned long long *p, unsigne
     return (unsigned)(wv >> 32);
 }
 
+// A double as a pair of tagged words in one 16-byte access: the halo values of r. No fence orders them against anything:
+// whoever finds both tags has the value.
+__device__ __forceinline__ void tl_store_tagged(unsigned long long *p, double v, unsigned tag) {
+    asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(tl_word(v, 0, tag)), "l"(tl_word(v, 1, tag)) : "memory");
+}
+__device__ __forceinline__ double tl_poll_tagged(const unsigned long long *p, unsigned tag, int *fail) {
+    unsigned long long a, b;
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+    if ((unsigned)a != tag || (unsigned)b != tag) {
+        const long long t0 = clock64();
+        int spins = 0;
+        for (;;) {
+            asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p) : "memory");
+            if ((unsigned)a == tag && (unsigned)b == tag) break;
+            if ((++spins & 63) == 0 && clock64() - t0 > 6000000000ll) {
+                *fail = 1;
+                break;
+            }
+        }
+    }
+    return __hiloint2double((int)(a >> 32), (int)(b >> 32));
+}
+
 // Sum over the whole grid and over all GPUs of NV <= 2 values per thread; every thread of every CTA of every GPU returns
 // with the same totals in v. wmask bit k: total k is an inner product, weighted by h1*h2 (S3:191) before it leaves the GPU.
-// publish: the CTA wrote global / peer memory that others read after this reduction (the r of its edge cells).
+// Nothing else is ordered by it: the halo values of r are tagged words themselves (tl_store_tagged), so no fence is needed.
 // False: a CTA or a peer GPU did not show up within the time limit -- the caller ends the solve.
 // (Measured: letting EVERY CTA gather all partials instead of CTA 0 saves a hop on paper and costs 4 us per iteration at
 // 148 CTAs -- 148 x 148 sector reads per polling round on the same few cache lines.)
 template <int NV>
 __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &A, const unsigned gen, const unsigned wmask,
-                                               const bool publish, double (*s_red)[TL_THREADS / 32], unsigned (*s_words)[TL_MAX_BLOCKS],
+                                               double (*s_red)[TL_THREADS / 32], unsigned (*s_words)[TL_MAX_BLOCKS],
                                                double *s_bc, int *s_fail, long long *stamp = nullptr) {
 #ifdef PB200_TILE_TIMING
 #define AR_STAMP(i) if (stamp) stamp[i] = clock64()
@@ -174,7 +193,6 @@ __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &
 #endif
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nblocks = gridDim.x, bid = blockIdx.x;
-    const bool sys = A.c.multi == 2;
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
         const double s = warp_sum(v[k]);
@@ -188,7 +206,6 @@ __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &
         double s = 0.0;
 #pragma unroll
         for (int q = 0; q < TL_THREADS / 32; ++q) s += s_red[k][q];
-        if (publish) tl_fence(sys); // release: the r of the edge cells (they may have gone to a peer GPU)
         *reinterpret_cast<volatile unsigned long long *>(&A.slots[(2 * k + (tid & 1)) * TL_MAX_BLOCKS + bid]) = tl_word(s, tid & 1, gen);
     }
     AR_STAMP(2);
@@ -210,7 +227,6 @@ __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &
                 s = ((wmask >> k) & 1u) ? s * A.c.h1 * A.c.h2 : s; // S3:191: sum * h1 * h2
                 tot[k] = __shfl_sync(0xffffffffu, s, 0);
             }
-            if (publish) tl_fence(sys);
             const int nw = A.pv.nranks * 2 * NV; // lane -> (destination rank, value, half)
             if (lane < nw) {
                 const int q = lane / (2 * NV), kh = lane - q * (2 * NV);
@@ -231,7 +247,6 @@ __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &
         }
         __syncwarp();
         AR_STAMP(6);
-        if (publish) tl_fence(sys); // acquire
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
             double s = 0.0;
@@ -328,6 +343,7 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
     // the thread's halo cells (loop-invariant): h < Ct: row above; < 2 Ct: row below; < 2 Ct + Rt: left column; else right column
     const int nh = 2 * Ct + 2 * Rt;
     int h_sm[TL_NH], h_gl[TL_NH];
+    unsigned h_live = 0u; // bit n: somebody (a neighbouring tile, a neighbouring GPU) rewrites that cell's r every iteration
 #pragma unroll
     for (int n = 0; n < TL_NH; ++n) {
         const int h = (TL_THREADS - 1 - tid) + n * TL_THREADS; // the threads without columns come first
@@ -338,6 +354,12 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
         else { hr = 1 + h - 2 * Ct - Rt; hc = Ct + 1; }
         h_sm[n] = (h < nh) ? hr * PC + hc + 1 : -1;
         h_gl[n] = hr * P + hc;
+        const int li = i_lo - 1 + hr, lj = j_lo - 1 + hc; // block-local: 0 and nx+1 / ny+1 are the block's ring
+        const bool live = (li == 0) ? A.pv.t_left != nullptr
+                        : (li == g.nx + 1) ? A.pv.t_right != nullptr
+                        : (lj == 0) ? A.pv.t_down != nullptr
+                        : (lj == g.ny + 1) ? A.pv.t_up != nullptr : true;
+        if (h < nh && live) h_live |= 1u << n;
     }
     __syncthreads();
 
@@ -362,7 +384,13 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
         // memory: ask for it first -- and on the own cells
         double r_halo[TL_NH];
 #pragma unroll
-        for (int n = 0; n < TL_NH; ++n) r_halo[n] = (h_sm[n] >= 0) ? __ldcg(&A.r[o00 + h_gl[n]]) : 0.0;
+        for (int n = 0; n < TL_NH; ++n) {
+            r_halo[n] = 0.0;
+            if (h_sm[n] >= 0) {
+                if (first || !((h_live >> n) & 1u)) r_halo[n] = __ldcg(&A.r[o00 + h_gl[n]]); // r = B (setup kernel); a physical boundary: 0
+                else r_halo[n] = tl_poll_tagged(A.r2 + 2 * (o00 + h_gl[n]), (unsigned)(k - 1), &s_fail);
+            }
+        }
         if (work) {
             int ip = ip0, ic = ic0;
             size_t og = og0;
@@ -470,9 +498,9 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
         TL_STAMP(2);
 #ifdef PB200_TILE_TIMING
         long long t_a1[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-        if (!tile_allreduce<1>(s1, A, (unsigned)(2 * k - 1), 1u, false, s_red, s_words, s_bc, &s_fail, t_rec ? t_a1 : nullptr)) {
+        if (!tile_allreduce<1>(s1, A, (unsigned)(2 * k - 1), 1u, s_red, s_words, s_bc, &s_fail, t_rec ? t_a1 : nullptr)) {
 #else
-        if (!tile_allreduce<1>(s1, A, (unsigned)(2 * k - 1), 1u, false, s_red, s_words, s_bc, &s_fail)) {
+        if (!tile_allreduce<1>(s1, A, (unsigned)(2 * k - 1), 1u, s_red, s_words, s_bc, &s_fail)) {
 #endif
             status = STOP_COMM_TIMEOUT;
             break;
@@ -519,22 +547,22 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
                     const bool row_edge = r == 0 || r == Rt - 1;
                     // the neighbouring tiles' halo (S4:361-398) and, on a block edge with a neighbour GPU, that GPU's ring (NVLink)
                     if (row_edge || col_edge0) {
-                        __stcg(&A.r[og], rn0);
+                        tl_store_tagged(A.r2 + 2 * og, rn0, (unsigned)k);
                         if (A.c.multi == 2) {
                             const int li = i_lo + r;
-                            if (li == 1 && A.pv.r_left) A.pv.r_left[(size_t)(A.pv.nx_left + 1) * P + lj] = rn0;
-                            if (li == g.nx && A.pv.r_right) A.pv.r_right[lj] = rn0;
-                            if (lj == 1 && A.pv.r_down) A.pv.r_down[(size_t)li * A.pv.pitch_down + A.pv.ny_down + 1] = rn0;
-                            if (lj == g.ny && A.pv.r_up) A.pv.r_up[(size_t)li * A.pv.pitch_up] = rn0;
+                            if (li == 1 && A.pv.t_left) tl_store_tagged(A.pv.t_left + 2 * ((size_t)(A.pv.nx_left + 1) * P + lj), rn0, (unsigned)k);
+                            if (li == g.nx && A.pv.t_right) tl_store_tagged(A.pv.t_right + 2 * (size_t)lj, rn0, (unsigned)k);
+                            if (lj == 1 && A.pv.t_down) tl_store_tagged(A.pv.t_down + 2 * ((size_t)li * A.pv.pitch_down + A.pv.ny_down + 1), rn0, (unsigned)k);
+                            if (lj == g.ny && A.pv.t_up) tl_store_tagged(A.pv.t_up + 2 * ((size_t)li * A.pv.pitch_up), rn0, (unsigned)k);
                         }
                     }
                     if (own1 && (row_edge || col_edge1)) {
-                        __stcg(&A.r[og + 1], rn1);
+                        tl_store_tagged(A.r2 + 2 * (og + 1), rn1, (unsigned)k);
                         if (A.c.multi == 2) {
                             const int li = i_lo + r;
-                            if (li == 1 && A.pv.r_left) A.pv.r_left[(size_t)(A.pv.nx_left + 1) * P + lj + 1] = rn1;
-                            if (li == g.nx && A.pv.r_right) A.pv.r_right[lj + 1] = rn1;
-                            if (lj + 1 == g.ny && A.pv.r_up) A.pv.r_up[(size_t)li * A.pv.pitch_up] = rn1;
+                            if (li == 1 && A.pv.t_left) tl_store_tagged(A.pv.t_left + 2 * ((size_t)(A.pv.nx_left + 1) * P + lj + 1), rn1, (unsigned)k);
+                            if (li == g.nx && A.pv.t_right) tl_store_tagged(A.pv.t_right + 2 * (size_t)(lj + 1), rn1, (unsigned)k);
+                            if (lj + 1 == g.ny && A.pv.t_up) tl_store_tagged(A.pv.t_up + 2 * ((size_t)li * A.pv.pitch_up), rn1, (unsigned)k);
                         }
                     }
                 }
@@ -542,9 +570,9 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
         }
         TL_STAMP(4);
 #ifdef PB200_TILE_TIMING
-        if (!tile_allreduce<2>(s2, A, (unsigned)(2 * k), 2u, true, s_red, s_words, s_bc, &s_fail, t_rec ? t_a : nullptr)) {
+        if (!tile_allreduce<2>(s2, A, (unsigned)(2 * k), 2u, s_red, s_words, s_bc, &s_fail, t_rec ? t_a : nullptr)) {
 #else
-        if (!tile_allreduce<2>(s2, A, (unsigned)(2 * k), 2u, true, s_red, s_words, s_bc, &s_fail)) {
+        if (!tile_allreduce<2>(s2, A, (unsigned)(2 * k), 2u, s_red, s_words, s_bc, &s_fail)) {
 #endif
             status = STOP_COMM_TIMEOUT;
             break;
