@@ -5,13 +5,14 @@
 // A p' live in the CTA's shared memory (up to 227 KB on sm_100a: 1.3 M cells per GPU), the class bytes of its cells too;
 // only w stays in global memory (it is touched once per iteration, by its owner alone). Per iteration:
 //
-//   phase A  p' = D^-1 r + beta p' (S4:559, 675) on the tile AND on its halo ring: the halo cells' r is read from global
-//            memory (written there by the neighbouring tile, or by the neighbouring GPU through NVLink, during the previous
-//            iteration), their p' is this CTA's own previous halo value -- bit-identical to the owner's, so p' is never
-//            exchanged, only r (as in the marching kernels);
+//   phase A  p' = z + beta p' (S4:675) on the tile AND on its halo ring, z = D^-1 r (S4:559). The own cells' z was left in
+//            shared memory by phase C of the previous iteration; the halo cells' z arrives as tagged words from the tile (or,
+//            through NVLink, the GPU) that owns them, and their p' is this CTA's own previous halo value -- bit-identical to
+//            the owner's, so p' is never exchanged (as in the marching kernels). Only iteration 1 divides here.
 //   phase B  A p' from shared memory (S4:526-535), kept in shared memory; (A p', p')     -> all-reduce 1
-//   phase C  w += alpha p', r -= alpha A p', sum dw^2, z = D^-1 r, sum z r (S4:640-656, 920); the tile's edge cells' r go to
-//            global memory and, on a block edge with a neighbour GPU, straight into that GPU's ring    -> all-reduce 2
+//   phase C  w += alpha p', r -= alpha A p', sum dw^2, z = D^-1 r, sum z r (S4:640-656, 920); z takes A p's place in shared
+//            memory; the tile's edge cells' z go out as tagged words: to the neighbouring tiles and, on a block edge with a
+//            neighbour GPU, straight into that GPU's halo copy    -> all-reduce 2
 //   the scalar tail of the iteration (S4:893-906, 926-932) in every thread, identically.
 //
 // A thread owns a pair of adjacent columns of the tile and marches down its rows: p' of the current row and the fluxes
@@ -380,44 +381,52 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
         ++k; // S4:847-848
         const bool first = k == 1;
         TL_STAMP(0);
-        // ---- phase A: p' = D^-1 r + beta p' (S4:559, 675; first: p = z, S4:830) on the halo ring -- its r comes from global
-        // memory: ask for it first -- and on the own cells
-        double r_halo[TL_NH];
+        // ---- phase A: p' = z + beta p' (S4:675; first: p = z, S4:830) on the halo ring and on the own cells. z = D^-1 r (S4:559)
+        // of the own cells was left in sAp by phase C of the previous iteration (the same expression on the same r), the halo
+        // cells' z comes as tagged words from the tile / GPU that owns them; only iteration 1 divides here, r = B from setup.
+        double v_halo[TL_NH];
+        unsigned h_isz = 0u; // bit n: v_halo[n] is z already
 #pragma unroll
         for (int n = 0; n < TL_NH; ++n) {
-            r_halo[n] = 0.0;
+            v_halo[n] = 0.0;
             if (h_sm[n] >= 0) {
-                if (first || !((h_live >> n) & 1u)) r_halo[n] = __ldcg(&A.r[o00 + h_gl[n]]); // r = B (setup kernel); a physical boundary: 0
-                else r_halo[n] = tl_poll_tagged(A.r2 + 2 * (o00 + h_gl[n]), (unsigned)(k - 1), &s_fail);
+                if (first || !((h_live >> n) & 1u)) v_halo[n] = __ldcg(&A.r[o00 + h_gl[n]]); // r = B (setup kernel); a physical boundary: 0
+                else {
+                    v_halo[n] = tl_poll_tagged(A.r2 + 2 * (o00 + h_gl[n]), (unsigned)(k - 1), &s_fail);
+                    h_isz |= 1u << n;
+                }
             }
         }
         if (work) {
             int ip = ip0, ic = ic0;
             size_t og = og0;
-            for (int r = r0; r < r1; ++r, ip += PC, ic += Cp, og += P) {
-                const double2 rv = lds2(sR + ic);
-                const unsigned kd2 = *reinterpret_cast<const unsigned short *>(sD + ip), kd0 = kd2 & 0xffu, kd1 = kd2 >> 8;
-                double z0, z1;
-                tl_precond2(rv.x, rv.y, kd0, kd1, s_lut, sHk, sHv, ip, A.D + og, safe, z0, z1); // S4:559
-                if (!first) {
-                    const double2 po = lds2(sP + ip);
-                    z0 = z0 + beta * po.x;
-                    z1 = z1 + beta * po.y;
+            if (first) {
+                for (int r = r0; r < r1; ++r, ip += PC, ic += Cp, og += P) {
+                    const double2 rv = lds2(sR + ic);
+                    const unsigned kd2 = *reinterpret_cast<const unsigned short *>(sD + ip), kd0 = kd2 & 0xffu, kd1 = kd2 >> 8;
+                    double z0, z1;
+                    tl_precond2(rv.x, rv.y, kd0, kd1, s_lut, sHk, sHv, ip, A.D + og, safe, z0, z1); // S4:559
+                    if (own0) sts2(sP + ip, z0, z1, own1);
                 }
-                if (own0) sts2(sP + ip, z0, z1, own1);
+            } else {
+                for (int r = r0; r < r1; ++r, ip += PC, ic += Cp) {
+                    const double2 z = lds2(sAp + ic), po = lds2(sP + ip);
+                    if (own0) sts2(sP + ip, z.x + beta * po.x, z.y + beta * po.y, own1);
+                }
             }
         }
 #pragma unroll
         for (int n = 0; n < TL_NH; ++n)
             if (h_sm[n] >= 0) {
                 const int ip = h_sm[n];
-                const unsigned kd = sD[ip];
-                const double2 DR = s_lut[kd];
-                const double rv = r_halo[n];
-                double z;
-                if (safe || kd == DCLS_GENERAL || !in_div_range(rv))
-                    z = precond_div(rv, kd == DCLS_GENERAL ? tl_lookup(sHk, sHv, tl_key(ip, 0u), A.D + o00 + h_gl[n]) : DR.x);
-                else z = div_const_nocheck(rv, DR.x, DR.y);
+                double z = v_halo[n];
+                if (!((h_isz >> n) & 1u)) {
+                    const unsigned kd = sD[ip];
+                    const double2 DR = s_lut[kd];
+                    if (safe || kd == DCLS_GENERAL || !in_div_range(z))
+                        z = precond_div(z, kd == DCLS_GENERAL ? tl_lookup(sHk, sHv, tl_key(ip, 0u), A.D + o00 + h_gl[n]) : DR.x);
+                    else z = div_const_nocheck(z, DR.x, DR.y);
+                }
                 sP[ip] = first ? z : z + beta * sP[ip];
             }
         __syncthreads();
@@ -538,6 +547,7 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
                     __stcg(&A.w[og], wn0);
                     if (own1) __stcg(&A.w[og + 1], wn1);
                     sts2(sR + ic, rn0, rn1, own1);
+                    sts2(sAp + ic, z0, z1, own1); // A p' is used up: its place keeps z for the next iteration's p' 
                     s2[0] += d0 * d0;
                     s2[1] += z0 * rn0; // S4:594
                     if (own1) {
@@ -545,24 +555,25 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
                         s2[1] += z1 * rn1;
                     }
                     const bool row_edge = r == 0 || r == Rt - 1;
-                    // the neighbouring tiles' halo (S4:361-398) and, on a block edge with a neighbour GPU, that GPU's ring (NVLink)
+                    // the neighbouring tiles' halo (S4:361-398; what they need of r is z = D^-1 r) and, on a block edge with a neighbour
+                    // GPU, that GPU's ring (NVLink)
                     if (row_edge || col_edge0) {
-                        tl_store_tagged(A.r2 + 2 * og, rn0, (unsigned)k);
+                        tl_store_tagged(A.r2 + 2 * og, z0, (unsigned)k);
                         if (A.c.multi == 2) {
                             const int li = i_lo + r;
-                            if (li == 1 && A.pv.t_left) tl_store_tagged(A.pv.t_left + 2 * ((size_t)(A.pv.nx_left + 1) * P + lj), rn0, (unsigned)k);
-                            if (li == g.nx && A.pv.t_right) tl_store_tagged(A.pv.t_right + 2 * (size_t)lj, rn0, (unsigned)k);
-                            if (lj == 1 && A.pv.t_down) tl_store_tagged(A.pv.t_down + 2 * ((size_t)li * A.pv.pitch_down + A.pv.ny_down + 1), rn0, (unsigned)k);
-                            if (lj == g.ny && A.pv.t_up) tl_store_tagged(A.pv.t_up + 2 * ((size_t)li * A.pv.pitch_up), rn0, (unsigned)k);
+                            if (li == 1 && A.pv.t_left) tl_store_tagged(A.pv.t_left + 2 * ((size_t)(A.pv.nx_left + 1) * P + lj), z0, (unsigned)k);
+                            if (li == g.nx && A.pv.t_right) tl_store_tagged(A.pv.t_right + 2 * (size_t)lj, z0, (unsigned)k);
+                            if (lj == 1 && A.pv.t_down) tl_store_tagged(A.pv.t_down + 2 * ((size_t)li * A.pv.pitch_down + A.pv.ny_down + 1), z0, (unsigned)k);
+                            if (lj == g.ny && A.pv.t_up) tl_store_tagged(A.pv.t_up + 2 * ((size_t)li * A.pv.pitch_up), z0, (unsigned)k);
                         }
                     }
                     if (own1 && (row_edge || col_edge1)) {
-                        tl_store_tagged(A.r2 + 2 * (og + 1), rn1, (unsigned)k);
+                        tl_store_tagged(A.r2 + 2 * (og + 1), z1, (unsigned)k);
                         if (A.c.multi == 2) {
                             const int li = i_lo + r;
-                            if (li == 1 && A.pv.t_left) tl_store_tagged(A.pv.t_left + 2 * ((size_t)(A.pv.nx_left + 1) * P + lj + 1), rn1, (unsigned)k);
-                            if (li == g.nx && A.pv.t_right) tl_store_tagged(A.pv.t_right + 2 * (size_t)(lj + 1), rn1, (unsigned)k);
-                            if (lj + 1 == g.ny && A.pv.t_up) tl_store_tagged(A.pv.t_up + 2 * ((size_t)li * A.pv.pitch_up), rn1, (unsigned)k);
+                            if (li == 1 && A.pv.t_left) tl_store_tagged(A.pv.t_left + 2 * ((size_t)(A.pv.nx_left + 1) * P + lj + 1), z1, (unsigned)k);
+                            if (li == g.nx && A.pv.t_right) tl_store_tagged(A.pv.t_right + 2 * (size_t)(lj + 1), z1, (unsigned)k);
+                            if (lj + 1 == g.ny && A.pv.t_up) tl_store_tagged(A.pv.t_up + 2 * ((size_t)li * A.pv.pitch_up), z1, (unsigned)k);
                         }
                     }
                 }
