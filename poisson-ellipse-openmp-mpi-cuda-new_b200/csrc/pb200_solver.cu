@@ -262,7 +262,9 @@ bool tile_plan(int nx, int ny, int sms, size_t smem_max, int &R, int &C, int &tr
     want = std::max(1, std::min(want, TL_MAX_BLOCKS));
     double best = 1e300;
     bool found = false;
+    const char *force = std::getenv("PB200_TILE_TC"); // tuning: tiles across, instead of the cost model's choice
     for (int c_try = 1; c_try <= want; ++c_try) {
+        if (force && atoi(force) > 0 && c_try != atoi(force)) continue;
         const int r_try = std::min(want / c_try, nx);
         if (r_try < 1 || c_try > ny) continue;
         const int Rq = (nx + r_try - 1) / r_try, Cq = (ny + c_try - 1) / c_try;
