@@ -256,7 +256,7 @@ MarchPlan march_plan(int resident_blocks, int wn, int nx) {
 
 // Tiles of tile_loop_kernel: tr x tc tiles of at most R x C cells, one per CTA, at most one CTA per SM. Small blocks use
 // fewer CTAs (a barrier among few is cheaper than idle threads are useful): about one cell per thread at least.
-bool tile_plan(int nx, int ny, int sms, size_t smem_max, int &R, int &C, int &tr, int &tc) {
+bool tile_plan(int nx, int ny, int sms, size_t smem_max, int &R, int &C, int &tr, int &tc, bool lean) {
     const long long cells = static_cast<long long>(nx) * ny;
     int want = static_cast<int>(std::min<long long>(sms, (cells + TL_THREADS - 1) / TL_THREADS));
     want = std::max(1, std::min(want, TL_MAX_BLOCKS));
@@ -269,7 +269,7 @@ bool tile_plan(int nx, int ny, int sms, size_t smem_max, int &R, int &C, int &tr
         if (r_try < 1 || c_try > ny) continue;
         const int Rq = (nx + r_try - 1) / r_try, Cq = (ny + c_try - 1) / c_try;
         if (Cq > TL_MAXC || 2 * (Rq + Cq) > TL_NH * TL_THREADS) continue;
-        if (tile_smem_bytes(Rq, Cq) > smem_max) continue;
+        if (tile_smem_bytes(Rq, Cq, lean) > smem_max) continue;
         // cost: what the slowest warp does per phase -- a thread owns a pair of columns and marches down its share of the
         // rows (pb200_tile.cuh) -- times the warps that share the SM's issue slots, plus the halo ring (one p' each)
         const int npair = (Cq + 1) / 2, txp = ((npair + 31) / 32) * 32, ty = std::max(1, std::min(TL_THREADS / txp, Rq));
@@ -290,10 +290,10 @@ bool tile_plan(int nx, int ny, int sms, size_t smem_max, int &R, int &C, int &tr
 // Could this decomposition run the resident loop kernel? Decided on the LARGEST block of the decomposition, so that every
 // rank gets the same answer (a rank in that kernel and its neighbour in the marching kernels would wait for each other
 // for ever).
-bool Solver::tile_feasible(int sms, size_t smem_max, int &R, int &C) const {
+bool Solver::tile_feasible(int sms, size_t smem_max, int &R, int &C, bool lean) const {
     const int nx_max = (prm.M - 1 + Px - 1) / Px, ny_max = (prm.N - 1 + Py - 1) / Py;
     int tr = 0, tc = 0;
-    return tile_plan(nx_max, ny_max, std::min(sms, TL_MAX_BLOCKS), smem_max, R, C, tr, tc);
+    return tile_plan(nx_max, ny_max, std::min(sms, TL_MAX_BLOCKS), smem_max, R, C, tr, tc, lean);
 }
 
 void Solver::plan_tile(int sms) {
@@ -309,32 +309,45 @@ void Solver::plan_tile(int sms) {
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
     cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     cudaFuncAttributes fa{};
-    if (!coop || cudaFuncGetAttributes(&fa, tile_loop_kernel) != cudaSuccess) {
+    if (!coop || cudaFuncGetAttributes(&fa, tile_loop_kernel<false>) != cudaSuccess) {
         cudaGetLastError();
         return;
     }
     const size_t smem_max = static_cast<size_t>(smem_optin) - fa.sharedSizeBytes;
     int R = 0, C = 0, tr = 0, tc = 0;
-    if (!tile_feasible(sms, smem_max, R, C) || !tile_r2) return;
+    if (!tile_r2) return;
+    // the form with everything in shared memory if the largest block fits it, else the lean one (PB200_TILE_LEAN=0: never,
+    // =1: always -- tuning / tests)
+    const char *env_lean = std::getenv("PB200_TILE_LEAN");
+    bool lean = env_lean && atoi(env_lean) == 1;
+    if (lean || !tile_feasible(sms, smem_max, R, C, false)) {
+        if (env_lean && atoi(env_lean) == 0) return;
+        if (!tile_feasible(sms, smem_max, R, C, true)) return;
+        lean = true;
+    }
     int R2 = 0, C2 = 0, tr2 = 0, tc2 = 0; // this rank's own block: its own best cut, else the largest block's tile size
-    if (tile_plan(f.g.nx, f.g.ny, std::min(sms, TL_MAX_BLOCKS), smem_max, R2, C2, tr2, tc2)) {
+    if (tile_plan(f.g.nx, f.g.ny, std::min(sms, TL_MAX_BLOCKS), smem_max, R2, C2, tr2, tc2, lean)) {
         R = R2;
         C = C2;
     }
     tr = (f.g.nx + R - 1) / R;
     tc = (f.g.ny + C - 1) / C;
-    const size_t smem = tile_smem_bytes(R, C);
-    if (cudaFuncSetAttribute(tile_loop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_max)) != cudaSuccess) {
+    const size_t smem = tile_smem_bytes(R, C, lean);
+    if (cudaFuncSetAttribute(tile_loop_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_max)) != cudaSuccess ||
+        cudaFuncSetAttribute(tile_loop_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_max)) != cudaSuccess) {
         cudaGetLastError();
         return;
     }
     int occ = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, tile_loop_kernel, TL_THREADS, smem) != cudaSuccess || occ < 1) {
+    const cudaError_t e_occ = lean ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, tile_loop_kernel<true>, TL_THREADS, smem)
+                                   : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, tile_loop_kernel<false>, TL_THREADS, smem);
+    if (e_occ != cudaSuccess || occ < 1) {
         cudaGetLastError();
         return;
     }
     if (static_cast<long long>(tr) * tc > static_cast<long long>(occ) * sms) return;
     use_tile = true;
+    tile_lean = lean;
     tile_R = R;
     tile_C = C;
     tile_tr = tr;
@@ -441,8 +454,8 @@ pb200_status Solver::create(const pb200_params &params) {
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
         cudaFuncAttributes fa{};
-        if (cudaFuncGetAttributes(&fa, tile_loop_kernel) == cudaSuccess && smem_optin > static_cast<int>(fa.sharedSizeBytes) &&
-            tile_feasible(sms, static_cast<size_t>(smem_optin) - fa.sharedSizeBytes, R, C)) {
+        if (cudaFuncGetAttributes(&fa, tile_loop_kernel<false>) == cudaSuccess && smem_optin > static_cast<int>(fa.sharedSizeBytes) &&
+            tile_feasible(sms, static_cast<size_t>(smem_optin) - fa.sharedSizeBytes, R, C, true)) {
             CK(cudaMalloc(&tile_r2, 2 * f.elems * sizeof(unsigned long long)));
             plan_launch(); // again, now that the kernel's halo buffer exists
         } else
@@ -614,6 +627,8 @@ pb200_status Solver::solve(pb200_result *res) {
         ta.cls = f.cls;
         ta.slots = tile_slots;
         ta.r2 = tile_r2;
+        ta.gz = f.p[0];
+        ta.gap = f.p[1];
         ta.trace = trace;
         ta.ctl = ctl;
         ta.g = f.g;
@@ -630,7 +645,9 @@ pb200_status Solver::solve(pb200_result *res) {
             ta.pv.mail[0] = mail;
         }
         void *args[] = {&ta};
-        CK(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(tile_loop_kernel), dim3(tile_tr * tile_tc, 1, 1),
+        CK(cudaLaunchCooperativeKernel(tile_lean ? reinterpret_cast<const void *>(tile_loop_kernel<true>)
+                                                 : reinterpret_cast<const void *>(tile_loop_kernel<false>),
+                                       dim3(tile_tr * tile_tc, 1, 1),
                                        dim3(TL_THREADS, 1, 1), args, tile_smem, stream));
         ++launches;
         k = c.max_iter + 1;

@@ -35,7 +35,7 @@ struct MarchPlan {
 MarchPlan march_plan(int resident_blocks, int wn, int nx);
 // tile_loop_kernel's cut of an nx x ny block for `sms` CTAs with `smem_max` bytes of dynamic shared memory each:
 // false if the block does not fit. R x C = tile size, tr x tc = tiles.
-bool tile_plan(int nx, int ny, int sms, size_t smem_max, int &R, int &C, int &tr, int &tc);
+bool tile_plan(int nx, int ny, int sms, size_t smem_max, int &R, int &C, int &tr, int &tc, bool lean = false);
 // single-GPU blocks of at most this many cells that do not fit cell_loop_kernel run cell_loop_stream_kernel (measured
 // cross-over with the marching kernels)
 constexpr double LOOP_STREAM_MAX_POINTS = 1.3e6;
@@ -81,7 +81,8 @@ struct Solver {
     size_t tile_smem = 0;
     unsigned long long *tile_slots = nullptr; // the CTAs' partial sums as tagged words
     unsigned long long *tile_r2 = nullptr;    // tagged copy of r (2 words per cell): the halo of the resident loop kernel
-    bool tile_feasible(int sms, size_t smem_max, int &R, int &C) const; // on the largest block: the same answer on every rank
+    bool tile_feasible(int sms, size_t smem_max, int &R, int &C, bool lean) const; // on the largest block: the same answer on every rank
+    bool tile_lean = false; // r and A p' / z in global memory (blocks of 1.1-2.9 M cells)
     long long launches = 0;
     long long last_iter = 0;
     double t_setup = 0.0;

@@ -50,6 +50,7 @@ struct TileArgs {
     unsigned long long *slots;  // TL_SLOT_WORDS tagged words, zeroed before every solve
     unsigned long long *r2;     // tagged copy of r, two words per stored cell (index 2 * (li * pitch + lj)), zeroed before every
                                 // solve: the tiles' edge cells travel through it (and through the neighbour GPUs' copies)
+    double *gz, *gap;           // lean form only: z and A p' of the own cells in global memory (the two p arrays, idle here)
     double *trace;
     Ctl *ctl;
     Geom g;
@@ -69,9 +70,12 @@ __host__ __device__ inline int tile_cp(int C) { return (C + 1) & ~1; }
 //   sHv, sHk   a hash table of TL_HASH exact values: the a, b, D of the cells cut by the ellipse ("general" class), so that the
 //        loop never waits for global memory (the gpu-scope fences of the all-reduce empty the L1 every iteration)
 constexpr int TL_HASH = 2048, TL_HASH_BITS = 11, TL_PROBES = 24;
-__host__ __device__ inline size_t tile_smem_bytes(int R, int C) {
+// lean: r and A p' / z stay in global memory (they are touched by their owner only and live in the L2); shared memory keeps
+// p' and the class bytes: 10 instead of 26 bytes per cell, for blocks of 1.1-2.9 M cells per GPU.
+__host__ __device__ inline size_t tile_smem_bytes(int R, int C, bool lean = false) {
     const size_t halo = (size_t)(R + 2) * (size_t)tile_pc(C), own = (size_t)R * (size_t)tile_cp(C);
-    return (halo + 2 * own) * sizeof(double) + ((halo + 15) / 16) * 16 + ((own + 15) / 16) * 16 + TL_HASH * (sizeof(double) + sizeof(unsigned));
+    return (halo + (lean ? 0 : 2 * own)) * sizeof(double) + ((halo + 15) / 16) * 16 + ((own + 15) / 16) * 16 +
+           TL_HASH * (sizeof(double) + sizeof(unsigned));
 }
 
 // key of an exact value: field 0 = D of the cell at haloed index i, 1 = a of the cell above compact index i,
@@ -272,6 +276,16 @@ __device__ __forceinline__ void sts2(double *p, double a, double b, bool both) {
     else *p = a;
 }
 
+// a thread's pair in global memory (lean form): two 8-byte accesses past L1, the second cell only where it is owned
+__device__ __forceinline__ double2 ldg2(const double *p, bool both) {
+    return make_double2(__ldcg(p), both ? __ldcg(p + 1) : 0.0);
+}
+__device__ __forceinline__ void stg2(double *p, double a, double b, bool both) {
+    __stcg(p, a);
+    if (both) __stcg(p + 1, b);
+}
+
+template <bool LEAN>
 __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs A) {
     extern __shared__ __align__(16) unsigned char tl_smem[];
     __shared__ double2 s_lut[16];
@@ -290,9 +304,9 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
     const int PC = tile_pc(A.C), Cp = tile_cp(A.C);
     const size_t n_halo = (size_t)(A.R + 2) * PC, n_own = (size_t)A.R * Cp;
     double *sP = reinterpret_cast<double *>(tl_smem);
-    double *sR = sP + n_halo;
+    double *sR = sP + n_halo;                       // (sR, sAp: not in the lean form)
     double *sAp = sR + n_own;
-    unsigned char *sD = reinterpret_cast<unsigned char *>(sAp + n_own);
+    unsigned char *sD = reinterpret_cast<unsigned char *>(LEAN ? sP + n_halo : sAp + n_own);
     unsigned char *sK = sD + ((n_halo + 15) / 16) * 16; // a(c) | a(up) << 2 | b(c) << 4 | b(right) << 6
     double *sHv = reinterpret_cast<double *>(sK + ((n_own + 15) / 16) * 16);
     unsigned *sHk = reinterpret_cast<unsigned *>(sHv + TL_HASH);
@@ -309,8 +323,10 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
         sD[q] = (unsigned char)DCLS_RING;
     }
     for (int q = tid; q < (int)n_own; q += TL_THREADS) {
-        sR[q] = 0.0;
-        sAp[q] = 0.0;
+        if (!LEAN) {
+            sR[q] = 0.0;
+            sAp[q] = 0.0;
+        }
         sK[q] = 0;
     }
     for (int q = tid; q < TL_HASH; q += TL_THREADS) sHk[q] = 0u;
@@ -330,7 +346,7 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
         if ((ku & 3u) == CLS_GENERAL) tl_insert(sHk, sHv, tl_key(lr * Cp + lc, 1u), A.a[o + P]);
         if (((kc >> 2) & 3u) == CLS_GENERAL) tl_insert(sHk, sHv, tl_key(lr * Cp + lc, 2u), A.b[o]);
         if (((kr >> 2) & 3u) == CLS_GENERAL) tl_insert(sHk, sHv, tl_key(lr * Cp + lc, 3u), A.b[o + 1]);
-        sR[lr * Cp + lc] = A.r[o]; // S4:813: r = B (setup / reset kernel)
+        if (!LEAN) sR[lr * Cp + lc] = A.r[o]; // S4:813: r = B (setup / reset kernel)
     }
     // Thread layout: a thread owns a PAIR of adjacent columns and marches down its rows; when the tile is narrow, TY groups
     // of threads share the rows. Lanes past the last pair shadow it (same reads, no stores, nothing summed), so that every
@@ -402,15 +418,15 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
             size_t og = og0;
             if (first) {
                 for (int r = r0; r < r1; ++r, ip += PC, ic += Cp, og += P) {
-                    const double2 rv = lds2(sR + ic);
+                    const double2 rv = LEAN ? ldg2(A.r + og, own1) : lds2(sR + ic);
                     const unsigned kd2 = *reinterpret_cast<const unsigned short *>(sD + ip), kd0 = kd2 & 0xffu, kd1 = kd2 >> 8;
                     double z0, z1;
                     tl_precond2(rv.x, rv.y, kd0, kd1, s_lut, sHk, sHv, ip, A.D + og, safe, z0, z1); // S4:559
                     if (own0) sts2(sP + ip, z0, z1, own1);
                 }
             } else {
-                for (int r = r0; r < r1; ++r, ip += PC, ic += Cp) {
-                    const double2 z = lds2(sAp + ic), po = lds2(sP + ip);
+                for (int r = r0; r < r1; ++r, ip += PC, ic += Cp, og += P) {
+                    const double2 z = LEAN ? ldg2(A.gz + og, own1) : lds2(sAp + ic), po = lds2(sP + ip);
                     if (own0) sts2(sP + ip, z.x + beta * po.x, z.y + beta * po.y, own1);
                 }
             }
@@ -494,7 +510,8 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
                 const double Ap0 = mih1 * (fxh0 - fxl0) + mih2 * (fm - fl); // S4:526-535
                 const double Ap1 = mih1 * (fxh1 - fxl1) + mih2 * (fr - fm);
                 if (own0) {
-                    sts2(sAp + ic, Ap0, Ap1, own1);
+                    if (LEAN) stg2(A.gap + og, Ap0, Ap1, own1);
+                    else sts2(sAp + ic, Ap0, Ap1, own1);
                     s1[0] += Ap0 * pc.x; // S4:594
                     if (own1) s1[0] += Ap1 * pc.y;
                 }
@@ -530,13 +547,23 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
             const int lj = j_lo + c0;
             const bool col_edge0 = c0 == 0 || c0 == Ct - 1, col_edge1 = c0 + 1 == Ct - 1; // first / last column of the tile
             double wa = own0 ? __ldcg(&A.w[og]) : 0.0, wb = own1 ? __ldcg(&A.w[og + 1]) : 0.0;
+            double2 g_r = make_double2(0.0, 0.0), g_ap = g_r; // lean form: r and A p' of the row come from global memory, a row ahead
+            if (LEAN && own0) {
+                g_r = ldg2(A.r + og, own1);
+                g_ap = ldg2(A.gap + og, own1);
+            }
             for (int r = r0; r < r1; ++r, ip += PC, ic += Cp, og += P) {
                 const double w0 = wa, w1 = wb;
+                const double2 rv = LEAN ? g_r : lds2(sR + ic), Ap = LEAN ? g_ap : lds2(sAp + ic);
                 if (r + 1 < r1) {
                     wa = own0 ? __ldcg(&A.w[og + P]) : 0.0;
                     wb = own1 ? __ldcg(&A.w[og + P + 1]) : 0.0;
+                    if (LEAN && own0) {
+                        g_r = ldg2(A.r + og + P, own1);
+                        g_ap = ldg2(A.gap + og + P, own1);
+                    }
                 }
-                const double2 pc = lds2(sP + ip), rv = lds2(sR + ic), Ap = lds2(sAp + ic);
+                const double2 pc = lds2(sP + ip);
                 const double wn0 = w0 + alpha * pc.x, wn1 = w1 + alpha * pc.y;       // S4:647
                 const double rn0 = rv.x - alpha * Ap.x, rn1 = rv.y - alpha * Ap.y;   // S4:648
                 const double d0 = wn0 - w0, d1 = wn1 - w1;                           // S4:653
@@ -546,8 +573,13 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
                 if (own0) {
                     __stcg(&A.w[og], wn0);
                     if (own1) __stcg(&A.w[og + 1], wn1);
-                    sts2(sR + ic, rn0, rn1, own1);
-                    sts2(sAp + ic, z0, z1, own1); // A p' is used up: its place keeps z for the next iteration's p' 
+                    if (LEAN) {
+                        stg2(A.r + og, rn0, rn1, own1);
+                        stg2(A.gz + og, z0, z1, own1);
+                    } else {
+                        sts2(sR + ic, rn0, rn1, own1);
+                        sts2(sAp + ic, z0, z1, own1); // A p' is used up: its place keeps z for the next iteration's p'
+                    }
                     s2[0] += d0 * d0;
                     s2[1] += z0 * rn0; // S4:594
                     if (own1) {
@@ -643,7 +675,7 @@ __global__ void __launch_bounds__(TL_THREADS, 1) tile_loop_kernel(const TileArgs
     for (int q = tid; q < Rt * Ct; q += TL_THREADS) {
         const int lr = q / Ct, lc = q - lr * Ct;
         const size_t o = o00 + (size_t)(lr + 1) * P + (lc + 1);
-        A.r[o] = sR[lr * Cp + lc];
+        if (!LEAN) A.r[o] = sR[lr * Cp + lc];
         p_out[o] = sP[(lr + 1) * PC + lc + 2];
     }
     if (bid == 0 && tid == 0) {
