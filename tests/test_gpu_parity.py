@@ -382,6 +382,37 @@ def test_tile_loop_kernel_shapes(monkeypatch, oracle, m, n, kw):
         np.testing.assert_allclose(w1, ow, rtol=0, atol=1e-11)
 
 
+@pytest.mark.parametrize("m,n,kw,force", [(130, 260, {}, True), (100, 140, {}, True), (400, 600, {}, True), (33, 1500, {}, True),
+                                          (2, 2, {}, True), (257, 130, {"eps": 1e-95, "fixed_iters": 12}, True),
+                                          (1200, 1600, {"fixed_iters": 60}, False), (1500, 1700, {"fixed_iters": 30}, False)])
+def test_tile_loop_kernel_lean_form(monkeypatch, oracle, m, n, kw, force):
+    """Blocks of 1.1-2.9 M cells per GPU run tile_loop_kernel in its lean form: p' and the class bytes in shared memory,
+    r and A p' / z in global memory, touched by their owner only (PB200_TILE_LEAN=1 forces that form on small blocks too).
+    Same arithmetic, same tagged-word exchange: against the two marching kernels and, where quick, the oracle."""
+    outs = []
+    for loop in ("1", "0"):
+        monkeypatch.setenv("PB200_LOOP", loop)
+        monkeypatch.setenv("PB200_TILE", "2")
+        if force:
+            monkeypatch.setenv("PB200_TILE_LEAN", "1")
+        with pb.Solver(pb.default_params(m, n, trace_len=8, **kw)) as s:
+            res = s.solve()
+            res2 = s.solve()          # again on the same handle (the scratch arrays are the two p arrays)
+            assert (res2.iterations, res2.zr, res2.w_norm_E) == (res.iterations, res.zr, res.w_norm_E)
+            outs.append((res, s.solution(), s.trace(8)))
+    (r1, w1, t1), (r0, w0, t0) = outs
+    assert r1.kernel_launches <= 4 < r0.kernel_launches or r0.iterations < 2
+    assert r0.iterations == r1.iterations and r0.stop_reason == r1.stop_reason and r0.safe_mode == r1.safe_mode
+    assert rel(r0.w_norm_E, r1.w_norm_E) < RTOL_NORM and rel(r0.diff_norm, r1.diff_norm) < 1e-9
+    assert rel(r0.r_norm_E, r1.r_norm_E) < 1e-9
+    np.testing.assert_allclose(t0, t1, rtol=1e-10, atol=0)
+    np.testing.assert_allclose(w0, w1, rtol=0, atol=1e-12)
+    if m * n <= 250000 and "eps" not in kw:
+        ores, ow, _ = oracle.solve(m, n, want_w=True)
+        assert r1.iterations == ores.iterations and rel(r1.w_norm_E, ores.w_norm_E) < RTOL_NORM
+        np.testing.assert_allclose(w1, ow, rtol=0, atol=1e-11)
+
+
 def test_resident_loop_first_iteration_bitwise(monkeypatch):
     """After ONE iteration p' (stored by the K1 phase) depends on no summed scalar: bit-identical between the marching
     kernels, the register-resident loop kernel and the shared-memory-resident one; w and r agree to the last bits of alpha."""
