@@ -153,11 +153,12 @@ pb200_status pb200_create(const pb200_params *p, pb200_solver **out);
  * (replaces MPI_Init/Comm_rank/Comm_size, S4:987-991). Collective over all ranks. */
 pb200_status pb200_comm_unique_id(uint8_t id_out[128]);
 pb200_status pb200_attach_comm(pb200_solver *s, const uint8_t unique_id[128]);
-/* Optional, after pb200_attach_comm: peer-memory mode. Each rank exports 256 bytes (where its mailbox and its residual
- * array live), the host gathers the exports of all ranks in rank order (replaces nothing in the reference: it would be
+/* Optional, after pb200_attach_comm: peer-memory mode. Each rank exports 256 bytes (where its mailbox, its residual
+ * array and the tagged halo copy of the resident loop kernel live), the host gathers the exports of all ranks in rank order (replaces nothing in the reference: it would be
  * an MPI_Allgather there) and every rank attaches them. From then on the two iteration kernels exchange halos and
  * partial sums themselves through NVLink stores into peer memory (CUDA IPC between processes, peer access between
- * threads) -- no NCCL call inside the loop, and the loop is replayed as a CUDA graph. Up to 8 ranks on one node.
+ * threads) -- no NCCL call inside the loop; blocks of up to ~2.9 M cells per GPU run the whole loop as one cooperative
+ * launch per rank, larger ones replay two kernels per iteration as a CUDA graph. Up to 8 ranks on one node.
  * Replaces exchange_halos_2d_gpu (S4:331-500) and the three MPI_Allreduce per iteration (S4:872, 893, 926). */
 pb200_status pb200_peer_export(pb200_solver *s, uint8_t blob_out[256]);
 pb200_status pb200_peer_attach(pb200_solver *s, const uint8_t *blobs_in_rank_order, int32_t nranks);
