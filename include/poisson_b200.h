@@ -182,7 +182,9 @@ void pb200_destroy(pb200_solver *s);
 /* One call = the reference binary's whole solver phase: create + solve (+ solution to host when
  * w_host != NULL, ld as above). Single rank. The handle is kept (one per host thread) so that an identical
  * next call reuses the device workspace and the coefficients instead of allocating and recomputing them;
- * any other call replaces it, pb200_release_cache() or the end of the thread frees it. */
+ * any other call replaces it, pb200_release_cache() or the end of the thread frees it. Call pb200_release_cache() yourself
+ * before the thread (or the process) ends: a workspace freed by the thread's own exit handlers may find the CUDA context
+ * already gone. */
 pb200_status pb200_run(const pb200_params *p, pb200_result *res, double *w_host, int64_t ld);
 void pb200_release_cache(void);
 
