@@ -384,7 +384,7 @@ def test_tile_loop_kernel_shapes(monkeypatch, oracle, m, n, kw):
 
 @pytest.mark.parametrize("m,n,kw,force", [(130, 260, {}, True), (100, 140, {}, True), (400, 600, {}, True), (33, 1500, {}, True),
                                           (2, 2, {}, True), (257, 130, {"eps": 1e-95, "fixed_iters": 12}, True),
-                                          (1200, 1600, {"fixed_iters": 60}, False), (1500, 1700, {"fixed_iters": 30}, False)])
+                                          (1200, 1600, {"fixed_iters": 60}, False), (1500, 1700, {"fixed_iters": 30}, False), (1600, 1200, {}, False)])
 def test_tile_loop_kernel_lean_form(monkeypatch, oracle, m, n, kw, force):
     """Blocks of 1.1-2.9 M cells per GPU run tile_loop_kernel in its lean form: p' and the class bytes in shared memory,
     r and A p' / z in global memory, touched by their owner only (PB200_TILE_LEAN=1 forces that form on small blocks too).
