@@ -286,8 +286,8 @@ bool tile_plan(int nx, int ny, int sms, size_t smem_max, int &R, int &C, int &tr
     for (size_t i = 1; i < cands.size(); ++i)
         if (cands[i].cost < cands[pick].cost) pick = i;
     if (lean) {
-        // The lean form is bound by the L2 (123 B per cell and iteration go through it), not by the SMs' issue slots: among
-        // the cuts within 15 % of the cheapest, the one that keeps the most SMs -- and their L2 ports -- busy. Measured at
+        // The lean form's time depends on the cut in ways the SM-side cost above does not capture (its r, z, A p' go through the
+        // L2): among the cuts within 15 % of the cheapest, the one that keeps the most SMs busy. Measured at
         // 1200 x 1600: 148 tiles of 33 x 400 cells 46 us per iteration, 145 tiles of 42 x 320 (the cheapest by the model) 63.
         const double limit = cands[pick].cost * 1.15;
         for (size_t i = 0; i < cands.size(); ++i)
