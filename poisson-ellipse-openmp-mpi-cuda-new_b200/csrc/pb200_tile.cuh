@@ -206,12 +206,15 @@ __device__ __forceinline__ bool tile_allreduce(double (&v)[NV], const TileArgs &
     AR_STAMP(0);
     __syncthreads();
     AR_STAMP(1);
-    if (tid < 2 * NV) { // one thread per word: the CTA's sum of value tid / 2, warps in index order
-        const int k = tid >> 1;
-        double s = 0.0;
+    if (warp == 0) { // the CTA's sums: a fixed tree over its 16 warps, one half-warp per value, then one lane per word
+        static_assert(TL_THREADS / 32 == 16 && NV <= 2, "a half-warp adds the 16 warps' partial sums of one value");
+        const int k = lane >> 4, j = lane & 15;
+        double s = (k < NV) ? s_red[k < NV ? k : 0][j] : 0.0;
 #pragma unroll
-        for (int q = 0; q < TL_THREADS / 32; ++q) s += s_red[k][q];
-        *reinterpret_cast<volatile unsigned long long *>(&A.slots[(2 * k + (tid & 1)) * TL_MAX_BLOCKS + bid]) = tl_word(s, tid & 1, gen);
+        for (int o = 8; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o, 16);
+        s = __shfl_sync(0xffffffffu, s, 0, 16);
+        if (k < NV && j < 2)
+            *reinterpret_cast<volatile unsigned long long *>(&A.slots[(2 * k + j) * TL_MAX_BLOCKS + bid]) = tl_word(s, j, gen);
     }
     AR_STAMP(2);
     if (bid == 0) { // gather the CTAs' partials, add them in CTA order, post the GPU's totals to every GPU
